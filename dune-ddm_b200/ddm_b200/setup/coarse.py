@@ -1,0 +1,107 @@
+"""Coarse space on the host (setup, runs once): GenEO basis and Galerkin matrix.
+
+GenEO follows /root/reference/dune/ddm/coarsespaces/coarse_spaces.hh:319-331:
+    A_neu v = lambda (D B_neu D) v,   smallest eigenvalues by shift-invert,
+then finalize_eigenvectors (:53-61: v <- D v, normalised to unit 2-norm) and zeroing at
+Dirichlet DOFs (/root/reference/examples/poisson.cc:235-238).  The reference drives
+Spectra's SymGEigsShiftSolver (/root/reference/dune/ddm/eigensolvers/spectra.hh:112-215,
+nev 16, ncv 2 nev, shift 1e-3, tolerance 1e-5, eigensolver_params.hh:43-51); Spectra needs
+Eigen, which is absent, so ARPACK's generalised shift-invert Lanczos (scipy eigsh, mode 3)
+plays that role.  Eigenvector signs/rotations are solver dependent; span(Z) is what
+matters.
+
+The Galerkin matrix is A0 = Z^T A Z in the reference's block ordering (offsets = exclusive
+scan of the per-rank basis sizes, /root/reference/dune/ddm/galerkin_preconditioner.hh:246-256).
+"""
+from __future__ import annotations
+
+import numpy as np
+import scipy.sparse as sp
+import scipy.sparse.linalg as spla
+
+
+def neumann_matrices(n, cells, Ke, sub, shared_count, dirichlet):
+    """A_neu (elements inside the subdomain) and B_neu (elements inside its overlap region),
+    both in the subdomain's local numbering, Dirichlet rows/cols eliminated."""
+    loc = -np.ones(n, dtype=np.int64)
+    loc[sub] = np.arange(sub.size)
+    lc = loc[cells]
+    inside = (lc >= 0).all(axis=1)
+    ovl_node = np.zeros(n, dtype=bool)
+    ovl_node[sub] = shared_count[sub] >= 2
+    in_ovl = inside & ovl_node[cells].all(axis=1)
+    k = cells.shape[1]
+
+    def asm(sel):
+        c = lc[sel]
+        rows = np.repeat(c, k, axis=1).ravel()
+        cols = np.tile(c, (1, k)).ravel()
+        M = sp.coo_matrix((Ke[sel].ravel(), (rows, cols)), shape=(sub.size, sub.size)).tocsr()
+        M.sum_duplicates()
+        return M
+
+    A_neu, B_neu = asm(inside), asm(in_ovl)
+    dl = dirichlet[sub]
+    free = sp.diags((~dl).astype(np.float64))
+    A_neu = (free @ A_neu @ free + sp.diags(dl.astype(np.float64))).tocsr()
+    B_neu = (free @ B_neu @ free).tocsr()
+    return A_neu, B_neu
+
+
+def geneo_basis(A_neu, B_neu, pou, dirichlet_local, nev=16, shift=1e-3, tol=1e-5, seed=1):
+    """Columns: pou-scaled, normalised eigenvectors for the nev smallest eigenvalues."""
+    n = A_neu.shape[0]
+    D = sp.diags(pou)
+    C = (D @ B_neu @ D).tocsc()
+    nev = min(nev, n - 2)
+    rng = np.random.default_rng(seed)
+    v0 = rng.standard_normal(n)
+    # Shift to the left of the spectrum (all eigenvalues are >= 0): A + shift*C is SPD-like
+    # and the eigenvalues nearest the shift are the smallest ones the reference asks for.
+    K = (A_neu + shift * C).tocsc()
+    lu = spla.splu(K, permc_spec="MMD_AT_PLUS_A", diag_pivot_thresh=0.0, options=dict(SymmetricMode=True))
+    OPinv = spla.LinearOperator((n, n), matvec=lu.solve, dtype=np.float64)
+    ncv = min(max(2 * nev, nev + 2), n - 1)
+    try:
+        w, V = spla.eigsh(A_neu.tocsc(), k=nev, M=C, sigma=-shift, which="LM", OPinv=OPinv, tol=tol, ncv=ncv, v0=v0, maxiter=1000)
+    except spla.ArpackNoConvergence as e:  # keep what converged, as the reference's retry loop would
+        w, V = e.eigenvalues, e.eigenvectors
+    order = np.argsort(w)
+    V = V[:, order]
+    V = V * pou[:, None]
+    V[dirichlet_local, :] = 0.0
+    nrm = np.linalg.norm(V, axis=0)
+    keep = nrm > 1e-14
+    V = V[:, keep] / nrm[keep]
+    return np.asfortranarray(V), w[order][keep]
+
+
+def pou_template_basis(coords_local, pou, dirichlet_local, degree=1):
+    """POU coarse space: pou * {1, x, y, (z), xy...} as in
+    /root/reference/dune/ddm/twolevel_schwarz.hh:47-51,107 (1, x, y, xy)."""
+    d = coords_local.shape[1]
+    cols = [np.ones(coords_local.shape[0])]
+    if degree >= 1:
+        for k in range(d):
+            cols.append(coords_local[:, k])
+        cols.append(np.prod(coords_local[:, :2], axis=1))
+    V = np.stack(cols, 1) * pou[:, None]
+    V[dirichlet_local, :] = 0.0
+    nrm = np.linalg.norm(V, axis=0)
+    V = V[:, nrm > 1e-14] / nrm[nrm > 1e-14]
+    return np.asfortranarray(V)
+
+
+def galerkin_matrix(A, subs, bases):
+    """Dense A0 = Z^T A Z, Z = [R_0^T Z_0 | R_1^T Z_1 | ...] and the column offsets."""
+    n = A.shape[0]
+    ks = np.array([b.shape[1] for b in bases], dtype=np.int64)
+    off = np.concatenate(([0], np.cumsum(ks)))
+    rows = np.concatenate([np.repeat(s[:, None], b.shape[1], 1).ravel() for s, b in zip(subs, bases)])
+    cols = np.concatenate(
+        [np.tile(np.arange(o, o + b.shape[1]), (s.size, 1)).ravel() for s, b, o in zip(subs, bases, off[:-1])]
+    )
+    vals = np.concatenate([np.ascontiguousarray(b).ravel() for b in bases])
+    Z = sp.coo_matrix((vals, (rows, cols)), shape=(n, int(off[-1]))).tocsr()
+    A0 = (Z.T @ (A @ Z)).toarray()
+    return A0, off, Z

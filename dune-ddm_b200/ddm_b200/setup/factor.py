@@ -1,0 +1,245 @@
+"""Sparse Cholesky factorisation of the subdomain matrices on the host (setup, runs once).
+
+The reference factors each overlapping Dirichlet matrix with CHOLMOD through
+Dune::Cholmod::setMatrix (/root/reference/extern/dune-istl/dune/istl/cholmod.hh:343-473,
+`cholmod_l_analyze` + `cholmod_l_factorize`).  SuiteSparse is a system dependency of the
+reference and is not available in this image, so the factorisation is restated here:
+nested-dissection ordering, supernodal symbolic analysis on the dissection tree and a
+multifrontal numeric phase.  The product is laid out exactly like a supernodal
+`cholmod_factor` (fields super / pi / px / s / x / Perm, LL^T, column-major panels that
+include the dense diagonal block), which is what the C ABI entry `ddm_upload_factor`
+takes -- a reference build would pass `Dune::Cholmod::cholmodFactor()` instead.
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass
+
+import numpy as np
+import scipy.linalg as sla
+import scipy.sparse as sp
+from scipy.linalg.blas import dtrsm as _dtrsm
+
+
+@dataclass
+class SupernodalFactor:
+    n: int
+    perm: np.ndarray  # int32[n]: perm[k] = original index of the k-th pivot (cholmod L->Perm)
+    super_: np.ndarray  # int32[nsuper+1]: first column of each supernode (L->super)
+    pi: np.ndarray  # int64[nsuper+1]: start of each supernode's row list in s (L->pi)
+    px: np.ndarray  # int64[nsuper+1]: start of each supernode's panel in x (L->px)
+    s: np.ndarray  # int32: row indices (pivot numbering), own columns first (L->s)
+    x: np.ndarray  # float64: column-major (nrow x ncol) panels (L->x)
+
+    @property
+    def nsuper(self):
+        return self.super_.size - 1
+
+    def nnz_panels(self):
+        return int(self.x.size)
+
+    def nnz_lower(self):
+        c = np.diff(self.super_).astype(np.int64)
+        r = np.diff(self.pi) - c
+        return int((c * (c + 1) // 2 + r * c).sum())
+
+
+# ----------------------------------------------------------------------------- ordering
+def _bfs_coordinate(indptr, indices, verts, inset):
+    """Pseudo-coordinate for graphs without geometry: BFS level from a far vertex."""
+    level = {}
+    start = verts[0]
+    for _ in range(2):
+        level = {int(start): 0}
+        front = [int(start)]
+        last = start
+        while front:
+            nxt = []
+            for v in front:
+                for u in indices[indptr[v] : indptr[v + 1]]:
+                    u = int(u)
+                    if inset[u] and u not in level:
+                        level[u] = level[v] + 1
+                        nxt.append(u)
+            if nxt:
+                last = nxt[-1]
+            front = nxt
+        start = last
+    far = max(level.values()) + 1 if level else 0
+    return np.array([level.get(int(v), far) for v in verts], dtype=np.float64)
+
+
+def nested_dissection(A, coords=None, leaf_size=32):
+    """Geometric nested dissection of the graph of symmetric A.
+
+    Returns (perm, blocks): `blocks` is the list of dissection-tree nodes in post-order,
+    each a contiguous range [first, last) of pivots; perm concatenates their vertices.
+    Separators are the vertices of the smaller side's boundary after a median split along
+    the longest axis of the current vertex set.
+    """
+    n = A.shape[0]
+    G = A.tocsr()
+    indptr, indices = G.indptr, G.indices
+    label = np.zeros(n, dtype=np.int8)
+    order: list[np.ndarray] = []
+
+    def rec(verts):
+        if verts.size <= leaf_size:
+            if verts.size:
+                order.append(verts)
+            return
+        if coords is not None:
+            pts = coords[verts]
+            ax = int(np.argmax(pts.max(0) - pts.min(0)))
+            key = pts[:, ax]
+        else:
+            label[verts] = 3
+            key = _bfs_coordinate(indptr, indices, verts, label)
+            label[verts] = 0
+        srt = np.lexsort((verts, key))
+        half = verts.size // 2
+        left, right = verts[srt[:half]], verts[srt[half:]]
+        label[left] = 1
+        label[right] = 2
+        # boundary of left towards right, and of right towards left
+        cnt = np.diff(indptr)
+        def boundary(side, other):
+            starts = indptr[side]
+            lens = cnt[side]
+            tot = int(lens.sum())
+            if tot == 0:
+                return np.zeros(side.size, dtype=bool)
+            offs = np.repeat(starts - np.concatenate(([0], np.cumsum(lens)[:-1])), lens) + np.arange(tot)
+            hit = label[indices[offs]] == other
+            seg = np.repeat(np.arange(side.size), lens)
+            return np.bincount(seg[hit], minlength=side.size) > 0
+        bl = boundary(left, 2)
+        br = boundary(right, 1)
+        label[verts] = 0
+        if bl.sum() <= br.sum():
+            sep, left = left[bl], left[~bl]
+        else:
+            sep, right = right[br], right[~br]
+        if sep.size == 0:  # disconnected halves
+            rec(left)
+            rec(right)
+            return
+        rec(left)
+        rec(right)
+        order.append(sep)
+
+    import sys
+
+    old = sys.getrecursionlimit()
+    sys.setrecursionlimit(max(old, 10000))
+    try:
+        rec(np.arange(n, dtype=np.int64))
+    finally:
+        sys.setrecursionlimit(old)
+    perm = np.concatenate(order) if order else np.zeros(0, dtype=np.int64)
+    first = np.concatenate(([0], np.cumsum([b.size for b in order]))).astype(np.int64)
+    return perm, first
+
+
+# ----------------------------------------------------------------------------- symbolic + numeric
+def cholesky_supernodal(A, coords=None, leaf_size=32):
+    """Supernodal LL^T of SPD A; one supernode per dissection-tree node."""
+    n = A.shape[0]
+    perm, first = nested_dissection(A, coords, leaf_size)
+    nsuper = first.size - 1
+    Ap = A.tocsr()[perm][:, perm].tocsr()
+    Ap.sort_indices()
+    indptr, indices, data = Ap.indptr, Ap.indices, Ap.data
+    col2super = np.repeat(np.arange(nsuper), np.diff(first))
+
+    # symbolic: struct(J) = (adj(J) u children's struct) \ {<= last column of J}
+    structs: list[np.ndarray] = [None] * nsuper  # type: ignore
+    parent = np.full(nsuper, -1, dtype=np.int64)
+    pending: list[list[int]] = [[] for _ in range(nsuper)]
+    for J in range(nsuper):
+        f, l = first[J], first[J + 1]
+        pieces = [indices[indptr[f] : indptr[l]]]
+        for c in pending[J]:
+            pieces.append(structs[c])
+        allidx = np.concatenate(pieces)
+        st = np.unique(allidx[allidx >= l])
+        structs[J] = st
+        if st.size:
+            parent[J] = col2super[st[0]]
+            pending[parent[J]].append(J)
+
+    ncol = np.diff(first)
+    nrow = ncol + np.array([s.size for s in structs], dtype=np.int64)
+    pi = np.concatenate(([0], np.cumsum(nrow))).astype(np.int64)
+    px = np.concatenate(([0], np.cumsum(nrow * ncol))).astype(np.int64)
+    s = np.empty(pi[-1], dtype=np.int32)
+    x = np.empty(px[-1], dtype=np.float64)
+
+    # numeric: multifrontal
+    loc = np.zeros(n, dtype=np.int64)
+    updates: dict[int, np.ndarray] = {}
+    for J in range(nsuper):
+        f, l = int(first[J]), int(first[J + 1])
+        c = l - f
+        st = structs[J]
+        m = c + st.size
+        idx = np.concatenate((np.arange(f, l), st))
+        s[pi[J] : pi[J + 1]] = idx
+        loc[idx] = np.arange(m)
+        F = np.zeros((m, m))
+        lo, hi = indptr[f], indptr[l]
+        cols = indices[lo:hi]
+        rows = np.repeat(np.arange(c), np.diff(indptr[f : l + 1]))
+        keep = cols >= f
+        F[loc[cols[keep]], rows[keep]] = data[lo:hi][keep]
+        for ch in pending[J]:
+            U = updates.pop(ch)
+            p = loc[structs[ch]]
+            F[np.ix_(p, p)] += U
+        try:
+            L11 = np.linalg.cholesky(F[:c, :c])
+        except np.linalg.LinAlgError as e:
+            raise np.linalg.LinAlgError(f"subdomain matrix not positive definite at supernode {J}") from e
+        panel = np.empty((m, c), order="F")
+        panel[:c] = L11
+        if m > c:
+            # X * L11^T = F21
+            L21 = _dtrsm(1.0, L11, F[c:, :c], side=1, lower=1, trans_a=1)
+            panel[c:] = L21
+            if parent[J] >= 0:
+                updates[J] = F[c:, c:] - L21 @ L21.T
+        x[px[J] : px[J + 1]] = panel.ravel(order="F")
+    return SupernodalFactor(
+        n=n,
+        perm=perm.astype(np.int32),
+        super_=first.astype(np.int32),
+        pi=pi,
+        px=px,
+        s=s,
+        x=x,
+    )
+
+
+def solve_supernodal(F: SupernodalFactor, b):
+    """Reference CPU solve with the factor (used by setup checks only, not the hot path)."""
+    y = np.asarray(b, dtype=np.float64)[F.perm].copy()
+    ns = F.nsuper
+    for J in range(ns):
+        f, l = F.super_[J], F.super_[J + 1]
+        c = l - f
+        rows = F.s[F.pi[J] : F.pi[J + 1]]
+        P = F.x[F.px[J] : F.px[J + 1]].reshape((rows.size, c), order="F")
+        y[f:l] = sla.solve_triangular(P[:c], y[f:l], lower=True, check_finite=False)
+        if rows.size > c:
+            y[rows[c:]] -= P[c:] @ y[f:l]
+    for J in range(ns - 1, -1, -1):
+        f, l = F.super_[J], F.super_[J + 1]
+        c = l - f
+        rows = F.s[F.pi[J] : F.pi[J + 1]]
+        P = F.x[F.px[J] : F.px[J + 1]].reshape((rows.size, c), order="F")
+        t = y[f:l]
+        if rows.size > c:
+            t = t - P[c:].T @ y[rows[c:]]
+        y[f:l] = sla.solve_triangular(P[:c], t, lower=True, trans="T", check_finite=False)
+    out = np.empty_like(y)
+    out[F.perm] = y
+    return out

@@ -1,0 +1,114 @@
+"""Finite-element assembly for the setup restatement (host side, runs once).
+
+Stands in for the PDELab assembly the reference does in
+/root/reference/examples/poisson.hh:279-319 (P1/Q1 ConvectionDiffusionFEM with a
+scalar permeability) and for the Dirichlet elimination of
+/root/reference/examples/pdelab_helper.hh:34-46 (Dirichlet rows become identity,
+Dirichlet columns are zeroed).
+"""
+from __future__ import annotations
+
+import numpy as np
+import scipy.sparse as sp
+
+
+# ----------------------------------------------------------------------------- coefficients
+def kappa_islands(x):
+    """Permeability of /root/reference/examples/poisson_coefficient.lua:9-36.
+
+    `x` is (m, d); for d = 3 the 2-D pattern is evaluated on (x, y) and the
+    checkerboard also alternates in z.
+    """
+    X, Y = x[:, 0], x[:, 1]
+    k = np.ones(x.shape[0])
+    m = (X > 0.3) & (X < 0.9) & (Y > 0.6 - (X - 0.3) / 6) & (Y < 0.8 - (X - 0.3) / 6)
+    k[m] = 1e5 * (X[m] + Y[m]) * 10.0
+    m = (X > 0.1) & (X < 0.5) & (Y > 0.1 + X) & (Y < 0.25 + X)
+    k[m] = 1e5 * (1.0 + 7.0 * Y[m])
+    m = (X > 0.5) & (X < 0.9) & (Y > 0.15 - (X - 0.5) * 0.25) & (Y < 0.35 - (X - 0.5) * 0.25)
+    k[m] = 1e5 * 2.5
+    ix = np.floor(15.0 * X).astype(np.int64)
+    iy = np.floor(15.0 * Y).astype(np.int64)
+    m = (ix % 2 == 0) & (iy % 2 == 0)
+    if x.shape[1] == 3:
+        iz = np.floor(15.0 * x[:, 2]).astype(np.int64)
+        m &= iz % 2 == 0
+        k[m] = 1e5 * (1.0 + ix[m] + iy[m] + iz[m])
+    else:
+        k[m] = 1e5 * (1.0 + ix[m] + iy[m])
+    return k
+
+
+def kappa_channels(x, contrast=1e6):
+    """High-permeability beams through the cube (config C5), after the channel
+    pattern of /root/reference/examples/poisson_problems.hh:62-95 extruded to 3-D."""
+    k = np.ones(x.shape[0])
+    fy = np.floor(8.0 * x[:, 1]).astype(np.int64)
+    fz = np.floor(8.0 * x[:, 2]).astype(np.int64) if x.shape[1] == 3 else np.zeros_like(fy)
+    m = (fy % 2 == 1) & (fz % 2 == 1)
+    k[m] = contrast
+    return k
+
+
+# ----------------------------------------------------------------------------- element matrices
+def p1_element_matrices(coords, cells, kappa):
+    """Stiffness matrices kappa * int grad phi_i . grad phi_j for simplices; (m, d+1, d+1)."""
+    d = coords.shape[1]
+    v = coords[cells]  # (m, d+1, d)
+    J = v[:, 1:, :] - v[:, :1, :]  # rows = edge vectors
+    det = np.linalg.det(J)
+    vol = np.abs(det) / {2: 2.0, 3: 6.0}[d]
+    Jinv = np.linalg.inv(J)  # (m, d, d); columns are gradients of phi_1..phi_d
+    G = np.empty((cells.shape[0], d + 1, d))
+    G[:, 1:, :] = np.transpose(Jinv, (0, 2, 1))
+    G[:, 0, :] = -G[:, 1:, :].sum(axis=1)
+    return (kappa * vol)[:, None, None] * np.einsum("mid,mjd->mij", G, G)
+
+
+def _q1_reference_matrix():
+    """8x8 Laplace stiffness of the unit cube (2-point Gauss), node order as structured_q1."""
+    gp = np.array([0.5 - 0.5 / np.sqrt(3.0), 0.5 + 0.5 / np.sqrt(3.0)])
+    K = np.zeros((8, 8))
+    corners = [(a, b, c) for a in (0, 1) for b in (0, 1) for c in (0, 1)]
+    for qx in gp:
+        for qy in gp:
+            for qz in gp:
+                g = np.zeros((8, 3))
+                for n, (a, b, c) in enumerate(corners):
+                    fx, dfx = (qx, 1.0) if a else (1 - qx, -1.0)
+                    fy, dfy = (qy, 1.0) if b else (1 - qy, -1.0)
+                    fz, dfz = (qz, 1.0) if c else (1 - qz, -1.0)
+                    g[n] = (dfx * fy * fz, fx * dfy * fz, fx * fy * dfz)
+                K += g @ g.T / 8.0
+    return K
+
+
+def q1_element_matrices(h, kappa):
+    """Q1 stiffness on cubes of edge h: kappa * h * K_ref; (m, 8, 8)."""
+    return (kappa * h)[:, None, None] * _q1_reference_matrix()[None]
+
+
+def assemble(n, cells, Ke, subset=None):
+    """Sum element matrices into an (n, n) CSR matrix (sorted columns, duplicates summed)."""
+    if subset is not None:
+        cells, Ke = cells[subset], Ke[subset]
+    k = cells.shape[1]
+    rows = np.repeat(cells, k, axis=1).ravel()
+    cols = np.tile(cells, (1, k)).ravel()
+    A = sp.coo_matrix((Ke.ravel(), (rows, cols)), shape=(n, n)).tocsr()
+    A.sum_duplicates()
+    A.sort_indices()
+    return A
+
+
+def eliminate_dirichlet(A, dirichlet):
+    """Identity rows / zero columns at constrained DOFs; pattern is kept.
+
+    Follows /root/reference/examples/pdelab_helper.hh:34-46.
+    """
+    A = A.tocsr().copy()
+    free = (~dirichlet).astype(np.float64)
+    Dfree = sp.diags(free)
+    A = (Dfree @ A @ Dfree + sp.diags(dirichlet.astype(np.float64))).tocsr()
+    A.sort_indices()
+    return A

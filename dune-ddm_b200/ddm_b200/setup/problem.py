@@ -1,0 +1,183 @@
+"""Builds the setup products of a two-level Schwarz solve on the host and stores them.
+
+This is the wiring order of the reference drivers
+(/root/reference/examples/poisson.cc:184-306 and /root/reference/examples/pdelab_schwarz.hh:36-180):
+grid -> assembly -> non-overlapping index set -> overlap growth -> overlapping Dirichlet
+matrices -> partition of unity -> subdomain factorisation -> coarse basis -> Galerkin matrix.
+Everything here runs once; the products are uploaded through the C ABI (include/ddm_b200.h)
+and the solve phase never comes back to this module.
+"""
+from __future__ import annotations
+
+import multiprocessing as mp
+import os
+from dataclasses import dataclass, field
+
+import numpy as np
+import scipy.sparse as sp
+
+from . import coarse as coarse_mod
+from . import decomp, factor, fem, mesh
+
+
+@dataclass
+class SetupProducts:
+    """Everything the solve phase needs (the ".ddmpack" content)."""
+
+    A: sp.csr_matrix  # global assembled, Dirichlet-eliminated operator on unique DOFs
+    b: np.ndarray  # right-hand side (assembled residual at the Dirichlet lift)
+    owner: np.ndarray  # int32[n] owning subdomain (lowest rank that sees the DOF)
+    subs: list  # per subdomain: int64 global ids of the overlapping index list (R_i)
+    pou: list  # per subdomain: float64 weights D_i
+    factors: list  # per subdomain: factor.SupernodalFactor of A_i = R_i A R_i^T
+    Z: list  # per subdomain: float64[n_i, k_i] (Fortran order) coarse basis
+    A0: np.ndarray  # dense Galerkin matrix Z^T A Z
+    coords: np.ndarray | None = None
+    dirichlet: np.ndarray | None = None
+    meta: dict = field(default_factory=dict)
+
+    @property
+    def n(self):
+        return self.A.shape[0]
+
+    @property
+    def nsub(self):
+        return len(self.subs)
+
+    def save(self, path):
+        d = dict(
+            A_indptr=self.A.indptr.astype(np.int64), A_indices=self.A.indices.astype(np.int32), A_data=self.A.data,
+            b=self.b, owner=self.owner, A0=self.A0, nsub=np.int64(self.nsub),
+            coords=self.coords if self.coords is not None else np.zeros((0, 0)),
+            dirichlet=self.dirichlet if self.dirichlet is not None else np.zeros(0, dtype=bool),
+            meta=np.array(repr(self.meta)),
+        )
+        for i in range(self.nsub):
+            F = self.factors[i]
+            d.update({f"sub{i}": self.subs[i], f"pou{i}": self.pou[i], f"Z{i}": self.Z[i],
+                      f"F{i}_perm": F.perm, f"F{i}_super": F.super_, f"F{i}_pi": F.pi, f"F{i}_px": F.px,
+                      f"F{i}_s": F.s, f"F{i}_x": F.x})
+        np.savez(path, **d)
+
+    @staticmethod
+    def load(path):
+        d = np.load(path, allow_pickle=False)
+        n = d["b"].size
+        A = sp.csr_matrix((d["A_data"], d["A_indices"], d["A_indptr"]), shape=(n, n))
+        ns = int(d["nsub"])
+        subs, pou, Z, factors = [], [], [], []
+        for i in range(ns):
+            subs.append(d[f"sub{i}"]); pou.append(d[f"pou{i}"]); Z.append(np.asfortranarray(d[f"Z{i}"]))
+            factors.append(factor.SupernodalFactor(n=subs[-1].size, perm=d[f"F{i}_perm"], super_=d[f"F{i}_super"],
+                                                   pi=d[f"F{i}_pi"], px=d[f"F{i}_px"], s=d[f"F{i}_s"], x=d[f"F{i}_x"]))
+        import ast
+        return SetupProducts(A=A, b=d["b"], owner=d["owner"], subs=subs, pou=pou, factors=factors, Z=Z, A0=d["A0"],
+                             coords=d["coords"] if d["coords"].size else None,
+                             dirichlet=d["dirichlet"] if d["dirichlet"].size else None,
+                             meta=ast.literal_eval(str(d["meta"])))
+
+
+# ----------------------------------------------------------------------------- per-subdomain work (process pool)
+_G: dict = {}
+
+
+def _sub_job(i):
+    from threadpoolctl import threadpool_limits
+
+    with threadpool_limits(1):
+        g = _G
+        s = g["subs"][i]
+        A = g["A"]
+        Ai = A[s][:, s].tocsr()
+        Ai.sort_indices()
+        co = g["coords"][s] if g["coords"] is not None else None
+        F = factor.cholesky_supernodal(Ai, co, g["leaf_size"])
+        kind = g["coarse"]
+        dl = g["dirichlet"][s]
+        if kind == "geneo":
+            An, Bn = coarse_mod.neumann_matrices(A.shape[0], g["cells"], g["Ke"], s, g["shared"], g["dirichlet"])
+            Zi, ev = coarse_mod.geneo_basis(An, Bn, g["pou"][i], dl, nev=g["nev"], shift=g["shift"], tol=g["eig_tol"])
+        elif kind == "pou":
+            Zi = coarse_mod.pou_template_basis(g["coords"][s], g["pou"][i], dl)
+        elif kind == "none":
+            Zi = np.zeros((s.size, 0), order="F")
+        else:
+            raise ValueError(f"unknown coarse space {kind!r}")
+        return i, F, Zi
+
+
+def build(coords, cells, Ke, dirichlet, rhs, cell_part, nsub, overlap=2, pou_kind="distance", shrink=0,
+          coarse="geneo", nev=16, shift=1e-3, eig_tol=1e-5, leaf_size=32, workers=None, meta=None):
+    """Generic pipeline from an element-wise description to SetupProducts."""
+    n = coords.shape[0]
+    A_full = fem.assemble(n, cells, Ke)
+    A = fem.eliminate_dirichlet(A_full, dirichlet)
+    b = np.where(dirichlet, 0.0, rhs)
+    novlp, owner = decomp.nonoverlapping_sets(n, cells, cell_part, nsub)
+    subs = decomp.grow_overlap(A_full, novlp, overlap)
+    bmasks = decomp.boundary_masks(A_full, subs)
+    pou = decomp.partition_of_unity(A_full, subs, bmasks, owner, pou_kind, shrink, overlap)
+    shared = np.zeros(n, dtype=np.int32)
+    for s in subs:
+        shared[s] += 1
+    _G.clear()
+    _G.update(A=A, subs=subs, coords=coords, cells=cells, Ke=Ke, dirichlet=dirichlet, shared=shared, pou=pou,
+              coarse=coarse, nev=nev, shift=shift, eig_tol=eig_tol, leaf_size=leaf_size)
+    workers = workers or min(nsub, os.cpu_count() or 1)
+    factors = [None] * nsub
+    Z = [None] * nsub
+    if workers > 1:
+        with mp.get_context("fork").Pool(workers) as pool:
+            for i, F, Zi in pool.imap_unordered(_sub_job, range(nsub)):
+                factors[i], Z[i] = F, Zi
+    else:
+        for i in range(nsub):
+            _, factors[i], Z[i] = _sub_job(i)
+    _G.clear()
+    A0, off, _ = coarse_mod.galerkin_matrix(A, subs, Z)
+    m = dict(meta or {})
+    m.update(nsub=nsub, overlap=overlap, pou=pou_kind, coarse=coarse, nev=nev, n=int(n), N0=int(A0.shape[0]))
+    return SetupProducts(A=A, b=b, owner=owner, subs=subs, pou=pou, factors=factors, Z=Z, A0=A0, coords=coords,
+                         dirichlet=dirichlet, meta=m)
+
+
+# ----------------------------------------------------------------------------- named configurations
+def poisson_simplex(coords, cells, nsub, kappa_fn=fem.kappa_islands, **kw):
+    """P1 Poisson with Dirichlet data g = 1 - x on x in {0, 1} (poisson_coefficient.lua:1-3,38-44)."""
+    d = coords.shape[1]
+    cent = coords[cells].mean(axis=1)
+    Ke = fem.p1_element_matrices(coords, cells, kappa_fn(cent))
+    dirichlet = (coords[:, 0] < 1e-6) | (coords[:, 0] > 1.0 - 1e-6)
+    n = coords.shape[0]
+    # residual at the Dirichlet lift x0 (g on the boundary, 0 inside): d = A_full x0 - f, f = 0
+    x0 = np.where(dirichlet, 1.0 - coords[:, 0], 0.0)
+    rhs = fem.assemble(n, cells, Ke) @ x0
+    part = decomp.rcb_partition(cent, nsub)
+    meta = dict(kw.pop("meta", {}), problem="poisson-p1", dim=d)
+    return build(coords, cells, Ke, dirichlet, rhs, part, nsub, meta=meta, **kw)
+
+
+def poisson_q1_cube(ncell, pgrid, kappa_fn=fem.kappa_channels, **kw):
+    """Structured Q1 Poisson on the unit cube, brick decomposition (config C5 family)."""
+    shape = (ncell,) * 3
+    coords, cells = mesh.structured_q1(shape)
+    cent = coords[cells].mean(axis=1)
+    Ke = fem.q1_element_matrices(1.0 / ncell, kappa_fn(cent))
+    dirichlet = (coords[:, 0] < 1e-9) | (coords[:, 0] > 1.0 - 1e-9)
+    x0 = np.where(dirichlet, 1.0 - coords[:, 0], 0.0)
+    rhs = fem.assemble(coords.shape[0], cells, Ke) @ x0
+    part = decomp.box_partition(shape, pgrid)
+    nsub = int(np.prod(pgrid))
+    meta = dict(kw.pop("meta", {}), problem="poisson-q1", dim=3, ncell=ncell, pgrid=tuple(pgrid))
+    return build(coords, cells, Ke, dirichlet, rhs, part, nsub, meta=meta, **kw)
+
+
+def unitcube_p1(ncell, nsub, **kw):
+    """Config C2 stand-in that needs no mesh file: Kuhn-triangulated unit cube, islands coefficient."""
+    coords, cells = mesh.structured_simplices((ncell,) * 3)
+    return poisson_simplex(coords, cells, nsub, meta=dict(mesh=f"kuhn-{ncell}^3"), **kw)
+
+
+def unitsquare_p1(ncell, nsub, **kw):
+    coords, cells = mesh.structured_simplices((ncell,) * 2)
+    return poisson_simplex(coords, cells, nsub, meta=dict(mesh=f"kuhn-{ncell}^2"), **kw)
