@@ -32,6 +32,7 @@ class SetupProducts:
     factors: list  # per subdomain: factor.SupernodalFactor of A_i = R_i A R_i^T
     Z: list  # per subdomain: float64[n_i, k_i] (Fortran order) coarse basis
     A0: np.ndarray  # dense Galerkin matrix Z^T A Z
+    n_novlp: np.ndarray | None = None  # per subdomain: the first n_novlp entries of subs[i] are its non-overlapping DOFs
     coords: np.ndarray | None = None
     dirichlet: np.ndarray | None = None
     meta: dict = field(default_factory=dict)
@@ -47,7 +48,7 @@ class SetupProducts:
     def save(self, path):
         d = dict(
             A_indptr=self.A.indptr.astype(np.int64), A_indices=self.A.indices.astype(np.int32), A_data=self.A.data,
-            b=self.b, owner=self.owner, A0=self.A0, nsub=np.int64(self.nsub),
+            b=self.b, owner=self.owner, A0=self.A0, nsub=np.int64(self.nsub), n_novlp=np.asarray(self.n_novlp, dtype=np.int64),
             coords=self.coords if self.coords is not None else np.zeros((0, 0)),
             dirichlet=self.dirichlet if self.dirichlet is not None else np.zeros(0, dtype=bool),
             meta=np.array(repr(self.meta)),
@@ -72,6 +73,7 @@ class SetupProducts:
                                                    pi=d[f"F{i}_pi"], px=d[f"F{i}_px"], s=d[f"F{i}_s"], x=d[f"F{i}_x"]))
         import ast
         return SetupProducts(A=A, b=d["b"], owner=d["owner"], subs=subs, pou=pou, factors=factors, Z=Z, A0=d["A0"],
+                             n_novlp=d["n_novlp"],
                              coords=d["coords"] if d["coords"].size else None,
                              dirichlet=d["dirichlet"] if d["dirichlet"].size else None,
                              meta=ast.literal_eval(str(d["meta"])))
@@ -138,6 +140,7 @@ def build(coords, cells, Ke, dirichlet, rhs, cell_part, nsub, overlap=2, pou_kin
     m = dict(meta or {})
     m.update(nsub=nsub, overlap=overlap, pou=pou_kind, coarse=coarse, nev=nev, n=int(n), N0=int(A0.shape[0]))
     return SetupProducts(A=A, b=b, owner=owner, subs=subs, pou=pou, factors=factors, Z=Z, A0=A0, coords=coords,
+                         n_novlp=np.array([v.size for v in novlp], dtype=np.int64),
                          dirichlet=dirichlet, meta=m)
 
 

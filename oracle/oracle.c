@@ -1,0 +1,262 @@
+/* CPU ORACLE -- TEST INFRASTRUCTURE, NOT THE PRODUCT.
+ *
+ * Plain-C restatement of the solve-phase hot path of dune-ddm, used only as the checker in
+ * tests/, in __graft_entry__.smoke() and as bench.py's cpu_baseline / --impl reference leg.
+ * Nothing under dune-ddm_b200/ may call into this file.
+ *
+ * Parity status: the reference ships no test of the apply path, so the
+ * apply-path results are pinned by this restatement plus (a) the reference's own golden
+ * literals for the setup (tests/test_galerkin_coarse_matrix.cc, checked in tests/test_golden.py),
+ * (b) the residual identity ||A_i x_i - d_i|| <= 1e-12 ||d_i|| at the direct-solver boundary
+ * (SuiteSparse is an un-vendored, un-pinned system dependency of the reference:
+ * CMakeLists.txt:43), and (c) the reference's real Dune::CGSolver compiled from
+ * /root/reference (oracle/_ref, see oracle/Makefile).
+ *
+ * Vectors are indexed by unique global DOF; a reference rank's consistent local vector is the
+ * restriction of that vector to the rank's index list.
+ */
+#include <math.h>
+#include <stdint.h>
+#include <stdlib.h>
+#include <string.h>
+#ifdef _OPENMP
+#include <omp.h>
+#endif
+
+/* y = A x, row by row, columns ascending: BCRSMatrix::mv,
+ * /root/reference/extern/dune-istl/dune/istl/bcrsmatrix.hh:1641-1661 */
+void oracle_spmv(int64_t n, const int64_t *rowptr, const int32_t *col, const double *val, const double *x, double *y,
+                 int nthreads)
+{
+#pragma omp parallel for num_threads(nthreads) schedule(static)
+    for (int64_t i = 0; i < n; ++i) {
+        double acc = 0.0;
+        for (int64_t k = rowptr[i]; k < rowptr[i + 1]; ++k) acc += val[k] * x[col[k]];
+        y[i] = acc;
+    }
+}
+
+/* sum over unique DOFs of x*y, left to right: OwnerOverlapCopyCommunication::dot with the owner
+ * mask applied, /root/reference/extern/dune-istl/dune/istl/owneroverlapcopy.hh:398-416 */
+double oracle_dot(int64_t n, const double *x, const double *y)
+{
+    double s = 0.0;
+    for (int64_t i = 0; i < n; ++i) s += x[i] * y[i];
+    return s;
+}
+
+/* One subdomain solve x = A_i^{-1} b with a supernodal LL^T factor in cholmod_factor layout.
+ * Dune::Cholmod::apply (/root/reference/extern/dune-istl/dune/istl/cholmod.hh:263-306) calls
+ * cholmod_l_solve(CHOLMOD_A): permute, forward solve with L, backward solve with L^T, un-permute.
+ * The supernodal sweeps restate the published algorithm of CHOLMOD's cholmod_super_lsolve /
+ * cholmod_super_ltsolve for one right-hand side (dense triangular solve on the diagonal block,
+ * dense matrix-vector update with the rows below). */
+void oracle_super_solve(int32_t n, int32_t nsuper, const int32_t *super, const int64_t *pi, const int64_t *px,
+                        const int32_t *s, const double *x, const int32_t *perm, const double *b, double *out,
+                        double *work /* n */)
+{
+    double *y = work;
+    for (int32_t k = 0; k < n; ++k) y[k] = b[perm[k]];
+    for (int32_t J = 0; J < nsuper; ++J) {
+        const int32_t f = super[J], c = super[J + 1] - f;
+        const int64_t m = pi[J + 1] - pi[J];
+        const double *P = x + px[J];
+        const int32_t *rows = s + pi[J];
+        for (int32_t j = 0; j < c; ++j) {
+            const double yj = y[f + j] / P[j + (int64_t)j * m];
+            y[f + j] = yj;
+            const double *colj = P + (int64_t)j * m;
+            for (int32_t i = j + 1; i < c; ++i) y[f + i] -= colj[i] * yj;
+            for (int64_t i = c; i < m; ++i) y[rows[i]] -= colj[i] * yj;
+        }
+    }
+    for (int32_t J = nsuper - 1; J >= 0; --J) {
+        const int32_t f = super[J], c = super[J + 1] - f;
+        const int64_t m = pi[J + 1] - pi[J];
+        const double *P = x + px[J];
+        const int32_t *rows = s + pi[J];
+        for (int32_t j = c - 1; j >= 0; --j) {
+            const double *colj = P + (int64_t)j * m;
+            double acc = y[f + j];
+            for (int64_t i = c; i < m; ++i) acc -= colj[i] * y[rows[i]];
+            for (int32_t i = j + 1; i < c; ++i) acc -= colj[i] * y[f + i];
+            y[f + j] = acc / colj[j];
+        }
+    }
+    for (int32_t k = 0; k < n; ++k) out[perm[k]] = y[k];
+}
+
+/* Setup products of all subdomains, flat (see oracle/oracle.py for how they are packed). */
+typedef struct {
+    int32_t nsub;
+    int64_t n;              /* unique global DOFs */
+    const int64_t *sub_ptr; /* nsub+1 */
+    const int32_t *sub_dofs;/* R_i index lists */
+    const double *pou;      /* D_i, same layout as sub_dofs */
+    /* factors, one entry per subdomain */
+    const int32_t *nsuper;
+    const int32_t **super;
+    const int64_t **pi, **px;
+    const int32_t **s;
+    const double **x;
+    const int32_t **perm;
+    /* coarse space */
+    const int64_t *z_ptr;   /* nsub+1 offsets into Z (column-major n_i x k_i blocks) */
+    const int32_t *k_off;   /* nsub+1 exclusive scan of k_i */
+    const double *Z;
+    const double *A0chol;   /* dense lower Cholesky factor of A0, row-major N0 x N0 */
+    /* operator (for the multiplicative combine) */
+    const int64_t *rowptr;
+    const int32_t *col;
+    const double *val;
+} oracle_setup;
+
+/* SchwarzPreconditioner::apply, /root/reference/dune/ddm/schwarz.hh:115-149.
+ * restricted != 0: x = sum_i R_i^T D_i A_i^{-1} R_i d ; else x = sum_i R_i^T A_i^{-1} R_i d.
+ * The halo sums of addOwnerCopyToOwnerCopy are taken in ascending rank order. */
+void oracle_schwarz_apply(const oracle_setup *S, int restricted, const double *d, double *x, int nthreads)
+{
+    const int64_t tot = S->sub_ptr[S->nsub];
+    double *xo = (double *)malloc(sizeof(double) * (size_t)tot);
+#pragma omp parallel num_threads(nthreads)
+    {
+        double *dl = NULL, *wk = NULL;
+        int64_t cap = 0;
+#pragma omp for schedule(dynamic, 1)
+        for (int32_t i = 0; i < S->nsub; ++i) {
+            const int64_t o = S->sub_ptr[i], ni = S->sub_ptr[i + 1] - o;
+            if (ni > cap) { free(dl); free(wk); cap = ni; dl = malloc(sizeof(double) * cap); wk = malloc(sizeof(double) * cap); }
+            for (int64_t k = 0; k < ni; ++k) dl[k] = d[S->sub_dofs[o + k]]; /* restrict + copyOwnerToAll */
+            oracle_super_solve((int32_t)ni, S->nsuper[i], S->super[i], S->pi[i], S->px[i], S->s[i], S->x[i], S->perm[i], dl,
+                               xo + o, wk);
+            if (restricted && S->pou)
+                for (int64_t k = 0; k < ni; ++k) xo[o + k] *= S->pou[o + k];
+        }
+        free(dl); free(wk);
+    }
+    memset(x, 0, sizeof(double) * (size_t)S->n);
+    for (int32_t i = 0; i < S->nsub; ++i)
+        for (int64_t k = S->sub_ptr[i]; k < S->sub_ptr[i + 1]; ++k) x[S->sub_dofs[k]] += xo[k];
+    free(xo);
+}
+
+/* GalerkinPreconditioner::apply, /root/reference/dune/ddm/galerkin_preconditioner.hh:151-194:
+ * restrict, k_i dot products per rank, gather, solve with A0 (here: dense Cholesky, the
+ * reference uses a sparse direct solver on rank 0), scatter, prolongate, halo sum. */
+void oracle_coarse_apply(const oracle_setup *S, const double *d, double *x, int nthreads)
+{
+    const int32_t N0 = S->k_off[S->nsub];
+    double *d0 = (double *)calloc((size_t)N0 + 1, sizeof(double));
+#pragma omp parallel for num_threads(nthreads) schedule(dynamic, 1)
+    for (int32_t i = 0; i < S->nsub; ++i) {
+        const int64_t o = S->sub_ptr[i], ni = S->sub_ptr[i + 1] - o;
+        const int32_t ki = S->k_off[i + 1] - S->k_off[i];
+        const double *Zi = S->Z + S->z_ptr[i];
+        for (int32_t k = 0; k < ki; ++k) {
+            double acc = 0.0;
+            for (int64_t j = 0; j < ni; ++j) acc += Zi[(int64_t)k * ni + j] * d[S->sub_dofs[o + j]];
+            d0[S->k_off[i] + k] = acc;
+        }
+    }
+    /* L L^T y = d0 */
+    const double *L = S->A0chol;
+    for (int32_t i = 0; i < N0; ++i) {
+        double acc = d0[i];
+        for (int32_t j = 0; j < i; ++j) acc -= L[(int64_t)i * N0 + j] * d0[j];
+        d0[i] = acc / L[(int64_t)i * N0 + i];
+    }
+    for (int32_t i = N0 - 1; i >= 0; --i) {
+        double acc = d0[i];
+        for (int32_t j = i + 1; j < N0; ++j) acc -= L[(int64_t)j * N0 + i] * d0[j];
+        d0[i] = acc / L[(int64_t)i * N0 + i];
+    }
+    memset(x, 0, sizeof(double) * (size_t)S->n);
+    const int64_t tot = S->sub_ptr[S->nsub];
+    double *xo = (double *)malloc(sizeof(double) * (size_t)tot);
+#pragma omp parallel for num_threads(nthreads) schedule(dynamic, 1)
+    for (int32_t i = 0; i < S->nsub; ++i) {
+        const int64_t o = S->sub_ptr[i], ni = S->sub_ptr[i + 1] - o;
+        const int32_t ki = S->k_off[i + 1] - S->k_off[i];
+        const double *Zi = S->Z + S->z_ptr[i];
+        for (int64_t j = 0; j < ni; ++j) xo[o + j] = 0.0;
+        for (int32_t k = 0; k < ki; ++k) {
+            const double c = d0[S->k_off[i] + k];
+            for (int64_t j = 0; j < ni; ++j) xo[o + j] += c * Zi[(int64_t)k * ni + j];
+        }
+    }
+    for (int32_t i = 0; i < S->nsub; ++i)
+        for (int64_t k = S->sub_ptr[i]; k < S->sub_ptr[i + 1]; ++k) x[S->sub_dofs[k]] += xo[k];
+    free(xo);
+    free(d0);
+}
+
+/* CombinedPreconditioner::apply, /root/reference/dune/ddm/combined_preconditioner.hh:127-163.
+ * mode 0 additive: x = M1 d + M0 d; mode 1 multiplicative: x = M1 d; x += M0 (d - A x).
+ * with_coarse == 0 gives the one-level method. */
+void oracle_twolevel_apply(const oracle_setup *S, int restricted, int mode, int with_coarse, const double *d, double *x,
+                           int nthreads)
+{
+    oracle_schwarz_apply(S, restricted, d, x, nthreads);
+    if (!with_coarse) return;
+    double *xn = (double *)malloc(sizeof(double) * (size_t)S->n);
+    if (mode == 0) {
+        oracle_coarse_apply(S, d, xn, nthreads);
+    } else {
+        double *dn = (double *)malloc(sizeof(double) * (size_t)S->n);
+        oracle_spmv(S->n, S->rowptr, S->col, S->val, x, dn, nthreads);
+        for (int64_t i = 0; i < S->n; ++i) dn[i] = d[i] - dn[i];
+        oracle_coarse_apply(S, dn, xn, nthreads);
+        free(dn);
+    }
+    for (int64_t i = 0; i < S->n; ++i) x[i] += xn[i];
+    free(xn);
+}
+
+/* Dune::CGSolver::apply, /root/reference/extern/dune-istl/dune/istl/solvers.hh:279-340, with the
+ * stopping rule of Iteration::step (solver.hh:457-480): def < def0*reduction || def < 1e-30.
+ * b is overwritten by the defect, x holds the solution.  Returns the iteration count; *converged and
+ * the defect history (maxit+1 entries) are filled. */
+int oracle_pcg(const oracle_setup *S, int restricted, int mode, int with_coarse, double *x, double *b, double reduction,
+               int maxit, double *history, int *converged, int nthreads)
+{
+    const int64_t n = S->n;
+    double *p = malloc(sizeof(double) * n), *q = malloc(sizeof(double) * n);
+    oracle_spmv(n, S->rowptr, S->col, S->val, x, q, nthreads); /* applyscaleadd(-1,x,b) */
+    for (int64_t i = 0; i < n; ++i) b[i] -= q[i];
+    double def = sqrt(oracle_dot(n, b, b)), def0 = def;
+    history[0] = def;
+    int i = 0;
+    *converged = (def < def0 * reduction || def < 1e-30);
+    if (!*converged) {
+        oracle_twolevel_apply(S, restricted, mode, with_coarse, b, p, nthreads);
+        double rholast = oracle_dot(n, p, b);
+        for (i = 1; i <= maxit; ++i) {
+            oracle_spmv(n, S->rowptr, S->col, S->val, p, q, nthreads);
+            const double alpha = oracle_dot(n, p, q);
+            const double lambda = (def == 0.0) ? 0.0 : rholast / alpha;
+            for (int64_t k = 0; k < n; ++k) x[k] += lambda * p[k];
+            for (int64_t k = 0; k < n; ++k) b[k] -= lambda * q[k];
+            def = sqrt(oracle_dot(n, b, b));
+            history[i] = def;
+            *converged = (def < def0 * reduction || def < 1e-30);
+            if (*converged) break;
+            oracle_twolevel_apply(S, restricted, mode, with_coarse, b, q, nthreads);
+            const double rho = oracle_dot(n, q, b);
+            const double beta = (def == 0.0) ? 0.0 : rho / rholast;
+            for (int64_t k = 0; k < n; ++k) p[k] = beta * p[k] + q[k];
+            rholast = rho;
+        }
+        if (i > maxit) i = maxit;
+    }
+    free(p); free(q);
+    return i;
+}
+
+int oracle_max_threads(void)
+{
+#ifdef _OPENMP
+    return omp_get_max_threads();
+#else
+    return 1;
+#endif
+}
