@@ -1,0 +1,1110 @@
+// C ABI (include/ddm_b200.h) over the sm_100a kernels in kernels.cuh.
+// Host side of the library: context, uploads, factor re-layout, task schedules, orchestration of the
+// apply path and the device-resident PCG loop.  No CPU compute path exists behind these entry points.
+#include "../../include/ddm_b200.h"
+#include "kernels.cuh"
+
+#include <cooperative_groups.h>
+#include <cuda_runtime.h>
+#include <cusolverDn.h>
+#include <nccl.h>
+
+#include <algorithm>
+#include <chrono>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <map>
+#include <numeric>
+#include <string>
+#include <vector>
+
+using namespace ddm;
+
+// ------------------------------------------------------------------------------------------------ errors
+static thread_local std::string g_err;
+static int fail(const char *fmt, ...)
+{
+    char buf[1024];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    g_err = buf;
+    return 1;
+}
+#define CU(call)                                                                                         \
+    do {                                                                                                 \
+        cudaError_t e_ = (call);                                                                         \
+        if (e_ != cudaSuccess) return fail("%s:%d %s: %s", __FILE__, __LINE__, #call, cudaGetErrorString(e_)); \
+    } while (0)
+#define NC(call)                                                                                         \
+    do {                                                                                                 \
+        ncclResult_t e_ = (call);                                                                        \
+        if (e_ != ncclSuccess) return fail("%s:%d %s: %s", __FILE__, __LINE__, #call, ncclGetErrorString(e_)); \
+    } while (0)
+#define CK(call)                                                                                         \
+    do {                                                                                                 \
+        int e_ = (call);                                                                                 \
+        if (e_) return e_;                                                                               \
+    } while (0)
+
+extern "C" const char *ddm_last_error(void) { return g_err.c_str(); }
+extern "C" const char *ddm_version(void) { return "ddm_b200 0.1 (sm_100a)"; }
+
+// ------------------------------------------------------------------------------------------------ context
+struct SubFactor {
+    int32_t n = 0;
+    std::vector<int32_t> perm;
+    // chunks (block columns of width <= 32), in elimination order
+    std::vector<int32_t> col0, w, parent, level, ntiles;
+    std::vector<int64_t> tile_off;   // offset (doubles) of the chunk's first tile in `panel`
+    std::vector<int64_t> row_off;    // offset of the chunk's row list in `rowidx`
+    std::vector<int64_t> dinv_off;   // offset of the chunk's inverse diagonal block in `dinv`
+    double *panel = nullptr;         // device
+    int32_t *rowidx = nullptr;       // device (absolute W offsets, filled at finalize)
+    double *dinv = nullptr;          // device
+    std::vector<int32_t> rows_host;  // pivot-numbered rows, -1 padding (becomes rowidx)
+    int64_t panel_doubles = 0, nnz_lower = 0;
+    bool present = false;
+};
+
+struct TimerRec {
+    std::string name;
+    cudaEvent_t a, b;
+};
+
+struct ddm_ctx {
+    int device = 0;
+    int sm_count = 148;
+    cudaStream_t s = nullptr;
+    int64_t launches = 0;
+    // operator
+    int64_t n_own = 0, n_ghost = 0, nloc = 0, nnz = 0;
+    int32_t *rowptr = nullptr, *col = nullptr;
+    double *val = nullptr;
+    int spmv_group = 8;
+    // decomposition
+    int32_t nsub = 0;
+    std::vector<int64_t> sub_ptr;
+    std::vector<int32_t> sub_dofs;
+    std::vector<double> pou_host;
+    bool have_pou = false;
+    std::vector<SubFactor> fac;
+    // coarse
+    std::vector<int32_t> sub_k, koff;
+    std::vector<double> Z_host;
+    int32_t N0 = 0, k_offset = 0, kpad = 0;
+    double *A0 = nullptr, *A0inv = nullptr, *d0 = nullptr, *y0 = nullptr, *r0 = nullptr;
+    // finalized device schedules
+    bool finalized = false;
+    int64_t P = 0; // total positions (sum n_i)
+    int32_t *gidx = nullptr;
+    double *pouP = nullptr, *Zp = nullptr, *W = nullptr, *X = nullptr;
+    int64_t *zoff = nullptr;
+    int32_t *d_sub_n = nullptr, *d_sub_k = nullptr, *d_koff = nullptr, *seg_ptr = nullptr;
+    Segment *segs = nullptr;
+    int32_t nseg = 0;
+    double *cpartial = nullptr;
+    int32_t *dptr = nullptr, *dpos = nullptr;
+    TriTask *fwd_tasks = nullptr, *bwd_tasks = nullptr;
+    int32_t n_fwd = 0, n_bwd = 0, nchunks = 0;
+    int32_t *need = nullptr, *nslices = nullptr;
+    int *cnt = nullptr; // [2*nchunks + 2]: fwd counters, bwd counters, tickets
+    int tri_grid = 0;
+    int tpt = 4;
+    // reductions / scalars
+    int nred = 0;
+    double *partial = nullptr, *scal = nullptr; // scal[8] device scalars
+    double *h_scal = nullptr;                   // pinned
+    double *h_stage = nullptr;                  // pinned staging for *_host entry points (2*n_own)
+    ddm_vec *hv[3] = {nullptr, nullptr, nullptr};
+    ddm_vec *tmp[4] = {nullptr, nullptr, nullptr, nullptr};
+    // comm
+    ncclComm_t comm = nullptr;
+    int rank = 0, nranks = 1;
+    int32_t npeers = 0;
+    std::vector<int32_t> peers;
+    std::vector<int64_t> send_ptr, recv_ptr;
+    int32_t *send_idx = nullptr;
+    double *sendbuf = nullptr, *recvbuf = nullptr;
+    // stats / timers
+    std::map<std::string, double> stats;
+    bool timers_on = false;
+    std::vector<TimerRec> trecs;
+    std::map<std::string, std::pair<double, int64_t>> tacc;
+};
+
+struct ddm_vec {
+    ddm_ctx *ctx;
+    double *d;
+};
+
+#define LAUNCH(ctx, kern, grid, block, ...)                       \
+    do {                                                          \
+        kern<<<(grid), (block), 0, (ctx)->s>>>(__VA_ARGS__);      \
+        (ctx)->launches++;                                        \
+    } while (0)
+
+static inline int nblocks(int64_t n, int per = 256) { return (int)std::max<int64_t>(1, (n + per - 1) / per); }
+static inline int stream_grid(ddm_ctx *c, int64_t n)
+{
+    return (int)std::min<int64_t>(std::max<int64_t>(1, (n + 255) / 256), (int64_t)c->sm_count * 8);
+}
+
+struct ScopedTimer {
+    ddm_ctx *c;
+    size_t idx = (size_t)-1;
+    ScopedTimer(ddm_ctx *c_, const char *name) : c(c_)
+    {
+        if (!c->timers_on) return;
+        TimerRec r;
+        r.name = name;
+        cudaEventCreate(&r.a);
+        cudaEventCreate(&r.b);
+        cudaEventRecord(r.a, c->s);
+        c->trecs.push_back(r);
+        idx = c->trecs.size() - 1;
+    }
+    ~ScopedTimer()
+    {
+        if (idx != (size_t)-1) cudaEventRecord(c->trecs[idx].b, c->s);
+    }
+};
+
+template <class T>
+static int dev_upload(T **dst, const T *src, size_t count)
+{
+    CU(cudaMalloc((void **)dst, std::max<size_t>(count, 1) * sizeof(T)));
+    if (count) CU(cudaMemcpy(*dst, src, count * sizeof(T), cudaMemcpyHostToDevice));
+    return 0;
+}
+
+extern "C" int ddm_ctx_create(int device, ddm_ctx **out)
+{
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0)
+        return fail("ddm_b200 needs a CUDA device (sm_100a); none found: %s", cudaGetErrorString(e));
+    if (device < 0 || device >= ndev) return fail("device %d out of range (have %d)", device, ndev);
+    CU(cudaSetDevice(device));
+    ddm_ctx *c = new ddm_ctx();
+    c->device = device;
+    cudaDeviceProp prop;
+    CU(cudaGetDeviceProperties(&prop, device));
+    c->sm_count = prop.multiProcessorCount;
+    CU(cudaStreamCreateWithFlags(&c->s, cudaStreamNonBlocking));
+    c->nred = c->sm_count * 4;
+    CU(cudaMalloc((void **)&c->partial, sizeof(double) * c->nred));
+    CU(cudaMalloc((void **)&c->scal, sizeof(double) * 16));
+    CU(cudaMemset(c->scal, 0, sizeof(double) * 16));
+    CU(cudaMallocHost((void **)&c->h_scal, sizeof(double) * 16));
+    if (const char *e2 = getenv("DDM_TPT")) c->tpt = std::max(1, atoi(e2));
+    *out = c;
+    return 0;
+}
+
+static void free_factor(SubFactor &f)
+{
+    cudaFree(f.panel);
+    cudaFree(f.rowidx);
+    cudaFree(f.dinv);
+    f = SubFactor();
+}
+
+extern "C" int ddm_vec_destroy(ddm_vec *v);
+
+extern "C" int ddm_ctx_destroy(ddm_ctx *c)
+{
+    if (!c) return 0;
+    cudaSetDevice(c->device);
+    cudaStreamSynchronize(c->s);
+    for (auto &v : c->hv) ddm_vec_destroy(v);
+    for (auto &v : c->tmp) ddm_vec_destroy(v);
+    for (auto &f : c->fac) free_factor(f);
+    void *ptrs[] = {c->rowptr, c->col, c->val, c->A0, c->A0inv, c->d0, c->y0, c->r0, c->gidx, c->pouP, c->Zp, c->W, c->X,
+                    c->zoff, c->d_sub_n, c->d_sub_k, c->d_koff, c->seg_ptr, c->segs, c->cpartial, c->dptr, c->dpos,
+                    c->fwd_tasks, c->bwd_tasks, c->need, c->nslices, c->cnt, c->partial, c->scal, c->send_idx, c->sendbuf,
+                    c->recvbuf};
+    for (void *p : ptrs) cudaFree(p);
+    cudaFreeHost(c->h_scal);
+    cudaFreeHost(c->h_stage);
+    for (auto &r : c->trecs) {
+        cudaEventDestroy(r.a);
+        cudaEventDestroy(r.b);
+    }
+    if (c->comm) ncclCommDestroy(c->comm);
+    cudaStreamDestroy(c->s);
+    delete c;
+    return 0;
+}
+
+// ------------------------------------------------------------------------------------------------ comm
+extern "C" int ddm_comm_unique_id(uint8_t out[128])
+{
+    ncclUniqueId id;
+    NC(ncclGetUniqueId(&id));
+    static_assert(sizeof(ncclUniqueId) == 128, "ncclUniqueId size");
+    memcpy(out, &id, 128);
+    return 0;
+}
+
+extern "C" int ddm_comm_init(ddm_ctx *c, int rank, int nranks, const uint8_t uid[128])
+{
+    CU(cudaSetDevice(c->device));
+    c->rank = rank;
+    c->nranks = nranks;
+    if (nranks > 1) {
+        ncclUniqueId id;
+        memcpy(&id, uid, 128);
+        NC(ncclCommInitRank(&c->comm, nranks, id, rank));
+    }
+    return 0;
+}
+
+extern "C" int ddm_upload_halo(ddm_ctx *c, int32_t npeers, const int32_t *peers, const int64_t *send_ptr,
+                               const int32_t *send_idx, const int64_t *recv_ptr)
+{
+    CU(cudaSetDevice(c->device));
+    c->npeers = npeers;
+    c->peers.assign(peers, peers + npeers);
+    c->send_ptr.assign(send_ptr, send_ptr + npeers + 1);
+    c->recv_ptr.assign(recv_ptr, recv_ptr + npeers + 1);
+    if (c->recv_ptr[npeers] != c->n_ghost) return fail("halo plan covers %lld ghosts, operator has %lld", (long long)c->recv_ptr[npeers], (long long)c->n_ghost);
+    CK(dev_upload(&c->send_idx, send_idx, (size_t)c->send_ptr[npeers]));
+    CU(cudaMalloc((void **)&c->sendbuf, sizeof(double) * std::max<int64_t>(1, c->send_ptr[npeers])));
+    CU(cudaMalloc((void **)&c->recvbuf, sizeof(double) * std::max<int64_t>(1, c->send_ptr[npeers])));
+    return 0;
+}
+
+__global__ void pack_kernel(int64_t n, const int32_t *__restrict__ idx, const double *__restrict__ v, double *__restrict__ buf)
+{
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) buf[i] = v[idx[i]];
+}
+__global__ void unpack_add_kernel(int64_t n, const int32_t *__restrict__ idx, const double *__restrict__ buf, double *__restrict__ v)
+{
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) v[idx[i]] += buf[i];
+}
+
+// owners -> ghosts (copyOwnerToAll, owneroverlapcopy.hh:311-319)
+static int halo_forward(ddm_ctx *c, double *v)
+{
+    if (c->nranks == 1 || c->npeers == 0) return 0;
+    const int64_t ns = c->send_ptr[c->npeers];
+    if (ns) LAUNCH(c, pack_kernel, nblocks(ns), 256, ns, c->send_idx, v, c->sendbuf);
+    NC(ncclGroupStart());
+    for (int p = 0; p < c->npeers; ++p) {
+        const int64_t sc = c->send_ptr[p + 1] - c->send_ptr[p], rc = c->recv_ptr[p + 1] - c->recv_ptr[p];
+        if (sc) NC(ncclSend(c->sendbuf + c->send_ptr[p], sc, ncclDouble, c->peers[p], c->comm, c->s));
+        if (rc) NC(ncclRecv(v + c->n_own + c->recv_ptr[p], rc, ncclDouble, c->peers[p], c->comm, c->s));
+    }
+    NC(ncclGroupEnd());
+    return 0;
+}
+// ghosts -> owners, summed in fixed peer order (addOwnerCopyToOwnerCopy / addOwnerCopyToAll, :362-387)
+static int halo_reverse_add(ddm_ctx *c, double *v)
+{
+    if (c->nranks == 1 || c->npeers == 0) return 0;
+    NC(ncclGroupStart());
+    for (int p = 0; p < c->npeers; ++p) {
+        const int64_t sc = c->send_ptr[p + 1] - c->send_ptr[p], rc = c->recv_ptr[p + 1] - c->recv_ptr[p];
+        if (rc) NC(ncclSend(v + c->n_own + c->recv_ptr[p], rc, ncclDouble, c->peers[p], c->comm, c->s));
+        if (sc) NC(ncclRecv(c->recvbuf + c->send_ptr[p], sc, ncclDouble, c->peers[p], c->comm, c->s));
+    }
+    NC(ncclGroupEnd());
+    for (int p = 0; p < c->npeers; ++p) { // one launch per peer: duplicates across peers add in peer order
+        const int64_t sc = c->send_ptr[p + 1] - c->send_ptr[p];
+        if (sc) LAUNCH(c, unpack_add_kernel, nblocks(sc), 256, sc, c->send_idx + c->send_ptr[p], c->recvbuf + c->send_ptr[p], v);
+    }
+    return 0;
+}
+
+// ------------------------------------------------------------------------------------------------ uploads
+extern "C" int ddm_upload_operator(ddm_ctx *c, int64_t n_own, int64_t n_ghost, const int64_t *rowptr, const int32_t *col,
+                                   const double *val)
+{
+    CU(cudaSetDevice(c->device));
+    if (c->rowptr) return fail("operator already uploaded");
+    const int64_t nnz = rowptr[n_own];
+    if (nnz >= (int64_t)INT32_MAX) return fail("operator has %lld nonzeros; one GPU holds at most 2^31-1", (long long)nnz);
+    if (n_own + n_ghost >= (int64_t)INT32_MAX) return fail("too many local DOFs");
+    c->n_own = n_own;
+    c->n_ghost = n_ghost;
+    c->nloc = n_own + n_ghost;
+    c->nnz = nnz;
+    std::vector<int32_t> rp(n_own + 1);
+    for (int64_t i = 0; i <= n_own; ++i) rp[i] = (int32_t)rowptr[i];
+    CK(dev_upload(&c->rowptr, rp.data(), rp.size()));
+    CK(dev_upload(&c->col, col, (size_t)nnz));
+    CK(dev_upload(&c->val, val, (size_t)nnz));
+    const double mean = n_own ? (double)nnz / (double)n_own : 1.0;
+    c->spmv_group = mean <= 3 ? 2 : mean <= 6 ? 4 : mean <= 40 ? 8 : mean <= 96 ? 16 : 32;
+    if (const char *e = getenv("DDM_SPMV_GROUP")) c->spmv_group = atoi(e);
+    c->stats["spmv"] = 12.0 * nnz + 4.0 * (n_own + 1) + 16.0 * n_own;
+    c->stats["dot"] = 16.0 * n_own;
+    c->stats["axpy"] = 24.0 * n_own;
+    CU(cudaMallocHost((void **)&c->h_stage, sizeof(double) * std::max<int64_t>(1, 2 * n_own)));
+    return 0;
+}
+
+extern "C" int ddm_upload_decomposition(ddm_ctx *c, int32_t nsub, const int64_t *sub_ptr, const int32_t *sub_dofs,
+                                        const double *pou)
+{
+    if (c->nsub) return fail("decomposition already uploaded");
+    c->nsub = nsub;
+    c->sub_ptr.assign(sub_ptr, sub_ptr + nsub + 1);
+    c->sub_dofs.assign(sub_dofs, sub_dofs + sub_ptr[nsub]);
+    for (int32_t v : c->sub_dofs)
+        if (v < 0 || v >= c->nloc) return fail("subdomain index %d outside the local vector (%lld)", v, (long long)c->nloc);
+    c->have_pou = pou != nullptr;
+    if (pou) c->pou_host.assign(pou, pou + sub_ptr[nsub]);
+    c->fac.resize(nsub);
+    c->sub_k.assign(nsub, 0);
+    if (sub_ptr[nsub] >= (int64_t)INT32_MAX) return fail("too many subdomain positions for one GPU");
+    return 0;
+}
+
+extern "C" int ddm_upload_factor(ddm_ctx *c, int32_t sub, int32_t n, int32_t nsuper, const int32_t *super, const int64_t *pi,
+                                 const int64_t *px, const int32_t *s, const double *x, const int32_t *perm)
+{
+    CU(cudaSetDevice(c->device));
+    if (sub < 0 || sub >= c->nsub) return fail("factor for subdomain %d, but %d are hosted", sub, c->nsub);
+    if (n != c->sub_ptr[sub + 1] - c->sub_ptr[sub]) return fail("factor size %d != subdomain size %lld", n, (long long)(c->sub_ptr[sub + 1] - c->sub_ptr[sub]));
+    SubFactor &F = c->fac[sub];
+    if (F.present) free_factor(F);
+    F.n = n;
+    F.perm.assign(perm, perm + n);
+    std::vector<int32_t> col2chunk(n, -1);
+    std::vector<ConvTile> conv;
+    std::vector<double> linv, dinv;
+    int64_t tile_doubles = 0, nrows_tot = 0;
+    for (int32_t J = 0; J < nsuper; ++J) {
+        const int32_t f = super[J], l = super[J + 1], cw = l - f;
+        const int64_t m = pi[J + 1] - pi[J];
+        const double *Pn = x + px[J];
+        F.nnz_lower += (int64_t)cw * (cw + 1) / 2 + (m - cw) * cw;
+        for (int32_t c0 = 0; c0 < cw; c0 += 32) {
+            const int32_t w = std::min(32, cw - c0);
+            const int32_t K = (int32_t)F.col0.size();
+            const int64_t below = m - (c0 + w);
+            const int32_t nt = (int32_t)((below + 31) / 32);
+            F.col0.push_back(f + c0);
+            F.w.push_back(w);
+            F.ntiles.push_back(nt);
+            F.tile_off.push_back(tile_doubles);
+            F.row_off.push_back(nrows_tot);
+            F.dinv_off.push_back((int64_t)dinv.size());
+            for (int32_t j = 0; j < w; ++j) col2chunk[f + c0 + j] = K;
+            // rows below the chunk: rest of the supernode's columns, then its row structure
+            for (int64_t r = c0 + w; r < m; ++r) F.rows_host.push_back(r < cw ? f + (int32_t)r : s[pi[J] + r]);
+            for (int64_t r = below; r < (int64_t)nt * 32; ++r) F.rows_host.push_back(-1);
+            // L_KK^{-1} (lower, column-major) and Dinv = L_KK^{-T} L_KK^{-1}
+            const int64_t lo = (int64_t)linv.size();
+            linv.resize(lo + (size_t)w * w, 0.0);
+            double *Li = linv.data() + lo;
+            auto Lkk = [&](int a, int b) { return Pn[(int64_t)(c0 + b) * m + (c0 + a)]; };
+            for (int j = 0; j < w; ++j) {
+                const double djj = Lkk(j, j);
+                if (!(djj > 0.0)) return fail("factor of subdomain %d has a non-positive pivot", sub);
+                Li[(int64_t)j * w + j] = 1.0 / djj;
+                for (int i = j + 1; i < w; ++i) {
+                    double acc = 0.0;
+                    for (int k = j; k < i; ++k) acc += Lkk(i, k) * Li[(int64_t)j * w + k];
+                    Li[(int64_t)j * w + i] = -acc / Lkk(i, i);
+                }
+            }
+            const size_t d0 = dinv.size();
+            dinv.resize(d0 + (size_t)w * w);
+            for (int a = 0; a < w; ++a)
+                for (int b = 0; b <= a; ++b) {
+                    double acc = 0.0;
+                    for (int k = a; k < w; ++k) acc += Li[(int64_t)a * w + k] * Li[(int64_t)b * w + k];
+                    dinv[d0 + (size_t)b * w + a] = acc;
+                    dinv[d0 + (size_t)a * w + b] = acc;
+                }
+            for (int32_t t = 0; t < nt; ++t) {
+                ConvTile ct;
+                ct.src = px[J] + (int64_t)c0 * m + (c0 + w) + (int64_t)t * 32;
+                ct.dst = tile_doubles + (int64_t)t * 32 * w;
+                ct.linv = lo;
+                ct.ld = (int32_t)m;
+                ct.nrows = (int32_t)std::min<int64_t>(32, below - (int64_t)t * 32);
+                ct.w = w;
+                ct.pad = 0;
+                conv.push_back(ct);
+            }
+            tile_doubles += (int64_t)nt * 32 * w;
+            nrows_tot += (int64_t)nt * 32;
+        }
+    }
+    const int32_t nch = (int32_t)F.col0.size();
+    F.parent.assign(nch, -1);
+    F.level.assign(nch, 0);
+    for (int32_t K = 0; K < nch; ++K) {
+        if (F.ntiles[K] > 0) {
+            const int32_t r0 = F.rows_host[F.row_off[K]];
+            F.parent[K] = col2chunk[r0];
+            if (F.parent[K] <= K) return fail("factor of subdomain %d is not in elimination order", sub);
+        }
+    }
+    for (int32_t K = 0; K < nch; ++K)
+        if (F.parent[K] >= 0) F.level[F.parent[K]] = std::max(F.level[F.parent[K]], F.level[K] + 1);
+    F.panel_doubles = tile_doubles;
+    // device: raw panels (temporary) -> Lt tiles
+    double *raw = nullptr, *dlinv = nullptr;
+    ConvTile *dconv = nullptr;
+    CK(dev_upload(&raw, x, (size_t)px[nsuper]));
+    CK(dev_upload(&dlinv, linv.data(), linv.size()));
+    CK(dev_upload(&dconv, conv.data(), conv.size()));
+    CK(dev_upload(&F.dinv, dinv.data(), dinv.size()));
+    CU(cudaMalloc((void **)&F.panel, sizeof(double) * std::max<int64_t>(1, tile_doubles)));
+    if (!conv.empty()) {
+        const int64_t nt = (int64_t)conv.size();
+        LAUNCH(c, convert_tiles_kernel, nblocks(nt * 32), 256, nt, dconv, raw, dlinv, F.panel);
+    }
+    CU(cudaStreamSynchronize(c->s));
+    CU(cudaGetLastError());
+    cudaFree(raw);
+    cudaFree(dlinv);
+    cudaFree(dconv);
+    F.present = true;
+    c->finalized = false;
+    return 0;
+}
+
+extern "C" int ddm_upload_coarse(ddm_ctx *c, const int32_t *k, const double *Z, int32_t N0, int32_t k_offset, const double *A0)
+{
+    CU(cudaSetDevice(c->device));
+    if (!c->nsub) return fail("upload the decomposition before the coarse space");
+    c->sub_k.assign(k, k + c->nsub);
+    int64_t tot = 0;
+    for (int32_t i = 0; i < c->nsub; ++i) tot += (int64_t)k[i] * (c->sub_ptr[i + 1] - c->sub_ptr[i]);
+    c->Z_host.assign(Z, Z + tot);
+    c->N0 = N0;
+    c->k_offset = k_offset;
+    if (N0 <= 0) return 0;
+    CK(dev_upload(&c->A0, A0, (size_t)N0 * N0));
+    CK(dev_upload(&c->A0inv, A0, (size_t)N0 * N0));
+    CU(cudaMalloc((void **)&c->d0, sizeof(double) * N0));
+    CU(cudaMalloc((void **)&c->y0, sizeof(double) * N0));
+    CU(cudaMalloc((void **)&c->r0, sizeof(double) * N0));
+    // A0^{-1} by dense Cholesky (setup, once; the reference factors A0 with a sparse direct solver on rank 0,
+    // galerkin_preconditioner.hh:331-346).
+    cusolverDnHandle_t h;
+    if (cusolverDnCreate(&h) != CUSOLVER_STATUS_SUCCESS) return fail("cusolverDnCreate failed");
+    cusolverDnSetStream(h, c->s);
+    int lwork = 0, lwork2 = 0;
+    cusolverDnDpotrf_bufferSize(h, CUBLAS_FILL_MODE_LOWER, N0, c->A0inv, N0, &lwork);
+    cusolverDnDpotri_bufferSize(h, CUBLAS_FILL_MODE_LOWER, N0, c->A0inv, N0, &lwork2);
+    lwork = std::max(lwork, lwork2);
+    double *work = nullptr;
+    int *info = nullptr;
+    CU(cudaMalloc((void **)&work, sizeof(double) * std::max(1, lwork)));
+    CU(cudaMalloc((void **)&info, sizeof(int)));
+    int hinfo = 0;
+    cusolverStatus_t st = cusolverDnDpotrf(h, CUBLAS_FILL_MODE_LOWER, N0, c->A0inv, N0, work, lwork, info);
+    CU(cudaMemcpyAsync(&hinfo, info, sizeof(int), cudaMemcpyDeviceToHost, c->s));
+    CU(cudaStreamSynchronize(c->s));
+    if (st != CUSOLVER_STATUS_SUCCESS || hinfo != 0) return fail("coarse matrix is not positive definite (potrf info %d)", hinfo);
+    st = cusolverDnDpotri(h, CUBLAS_FILL_MODE_LOWER, N0, c->A0inv, N0, work, lwork, info);
+    CU(cudaMemcpyAsync(&hinfo, info, sizeof(int), cudaMemcpyDeviceToHost, c->s));
+    CU(cudaStreamSynchronize(c->s));
+    if (st != CUSOLVER_STATUS_SUCCESS || hinfo != 0) return fail("coarse inverse failed (potri info %d)", hinfo);
+    cudaFree(work);
+    cudaFree(info);
+    cusolverDnDestroy(h);
+    // potri fills one triangle: mirror it so rows can be streamed
+    std::vector<double> M((size_t)N0 * N0);
+    CU(cudaMemcpy(M.data(), c->A0inv, sizeof(double) * M.size(), cudaMemcpyDeviceToHost));
+    for (int i = 0; i < N0; ++i)
+        for (int j = 0; j < i; ++j) { // column-major lower (i>j) at M[j*N0+i]
+            M[(size_t)i * N0 + j] = M[(size_t)j * N0 + i];
+        }
+    CU(cudaMemcpy(c->A0inv, M.data(), sizeof(double) * M.size(), cudaMemcpyHostToDevice));
+    c->finalized = false;
+    return 0;
+}
+
+// ------------------------------------------------------------------------------------------------ finalize
+extern "C" int ddm_vec_create(ddm_ctx *c, ddm_vec **out);
+
+extern "C" int ddm_finalize(ddm_ctx *c)
+{
+    CU(cudaSetDevice(c->device));
+    if (!c->rowptr) return fail("upload the operator first");
+    for (int i = 0; i < 3; ++i)
+        if (!c->hv[i]) CK(ddm_vec_create(c, &c->hv[i]));
+    for (int i = 0; i < 4; ++i)
+        if (!c->tmp[i]) CK(ddm_vec_create(c, &c->tmp[i]));
+    if (c->nsub == 0) {
+        c->finalized = true;
+        return 0;
+    }
+    for (int32_t i = 0; i < c->nsub; ++i)
+        if (!c->fac[i].present) return fail("no factor uploaded for subdomain %d", i);
+    // release an earlier schedule
+    void *old[] = {c->gidx, c->pouP, c->Zp, c->W, c->X, c->zoff, c->d_sub_n, c->d_sub_k, c->d_koff, c->seg_ptr, c->segs,
+                   c->cpartial, c->dptr, c->dpos, c->fwd_tasks, c->bwd_tasks, c->need, c->nslices, c->cnt};
+    for (void *p : old) cudaFree(p);
+
+    const int32_t ns = c->nsub;
+    const int64_t P = c->sub_ptr[ns];
+    c->P = P;
+    // positions in pivot order
+    std::vector<int32_t> gidx(P);
+    std::vector<double> pouP(c->have_pou ? P : 0);
+    std::vector<int32_t> sub_n(ns);
+    for (int32_t i = 0; i < ns; ++i) {
+        const int64_t o = c->sub_ptr[i];
+        const SubFactor &F = c->fac[i];
+        sub_n[i] = F.n;
+        for (int32_t k = 0; k < F.n; ++k) {
+            gidx[o + k] = c->sub_dofs[o + F.perm[k]];
+            if (c->have_pou) pouP[o + k] = c->pou_host[o + F.perm[k]];
+        }
+    }
+    CK(dev_upload(&c->gidx, gidx.data(), gidx.size()));
+    if (c->have_pou) CK(dev_upload(&c->pouP, pouP.data(), pouP.size()));
+    else c->pouP = nullptr;
+    CU(cudaMalloc((void **)&c->W, sizeof(double) * std::max<int64_t>(1, P)));
+    CU(cudaMalloc((void **)&c->X, sizeof(double) * std::max<int64_t>(1, P)));
+    // coarse basis permuted to pivot order (column-major per subdomain)
+    c->koff.assign(ns + 1, 0);
+    std::vector<int64_t> zoff(ns + 1, 0);
+    int kmax = 0;
+    for (int32_t i = 0; i < ns; ++i) {
+        c->koff[i + 1] = c->koff[i] + c->sub_k[i];
+        zoff[i + 1] = zoff[i] + (int64_t)c->sub_k[i] * sub_n[i];
+        kmax = std::max(kmax, c->sub_k[i]);
+    }
+    std::vector<int32_t> koff_abs(ns + 1);
+    for (int32_t i = 0; i <= ns; ++i) koff_abs[i] = c->koff[i] + c->k_offset;
+    c->kpad = std::max(1, kmax);
+    if (c->N0 > 0) {
+        std::vector<double> Zp(zoff[ns]);
+        for (int32_t i = 0; i < ns; ++i) {
+            const SubFactor &F = c->fac[i];
+            for (int32_t kk = 0; kk < c->sub_k[i]; ++kk)
+                for (int32_t k = 0; k < F.n; ++k) Zp[zoff[i] + (int64_t)kk * F.n + k] = c->Z_host[zoff[i] + (int64_t)kk * F.n + F.perm[k]];
+        }
+        CK(dev_upload(&c->Zp, Zp.data(), Zp.size()));
+    } else
+        c->Zp = nullptr;
+    CK(dev_upload(&c->zoff, zoff.data(), zoff.size()));
+    CK(dev_upload(&c->d_sub_n, sub_n.data(), sub_n.size()));
+    CK(dev_upload(&c->d_sub_k, c->sub_k.data(), c->sub_k.size()));
+    CK(dev_upload(&c->d_koff, koff_abs.data(), koff_abs.size()));
+    // segments
+    std::vector<Segment> segs;
+    std::vector<int32_t> seg_ptr(ns + 1, 0);
+    for (int32_t i = 0; i < ns; ++i) {
+        const int64_t o = c->sub_ptr[i];
+        for (int32_t a = 0; a < sub_n[i]; a += kSeg) segs.push_back({i, (int32_t)(o + a), std::min(kSeg, sub_n[i] - a), a});
+        seg_ptr[i + 1] = (int32_t)segs.size();
+    }
+    c->nseg = (int32_t)segs.size();
+    CK(dev_upload(&c->segs, segs.data(), segs.size()));
+    CK(dev_upload(&c->seg_ptr, seg_ptr.data(), seg_ptr.size()));
+    CU(cudaMalloc((void **)&c->cpartial, sizeof(double) * std::max<int64_t>(1, (int64_t)c->nseg * c->kpad)));
+    // transpose of the restriction: positions per local DOF (ascending position = ascending subdomain)
+    {
+        std::vector<int32_t> dptr(c->nloc + 1, 0), dpos(P);
+        for (int64_t p = 0; p < P; ++p) dptr[gidx[p] + 1]++;
+        for (int64_t v = 0; v < c->nloc; ++v) dptr[v + 1] += dptr[v];
+        std::vector<int32_t> fillp(dptr.begin(), dptr.end() - 1);
+        for (int64_t p = 0; p < P; ++p) dpos[fillp[gidx[p]]++] = (int32_t)p;
+        CK(dev_upload(&c->dptr, dptr.data(), dptr.size()));
+        CK(dev_upload(&c->dpos, dpos.data(), dpos.size()));
+    }
+    // triangular-solve schedules
+    std::vector<int32_t> chunk_base(ns + 1, 0);
+    for (int32_t i = 0; i < ns; ++i) chunk_base[i + 1] = chunk_base[i] + (int32_t)c->fac[i].col0.size();
+    c->nchunks = chunk_base[ns];
+    std::vector<int32_t> need(c->nchunks, 0), nslices(c->nchunks, 0);
+    struct Key {
+        int32_t level;
+        int32_t sub, chunk, slice;
+    };
+    std::vector<Key> keys;
+    const int tpt = c->tpt;
+    double bytes_f = 0, bytes_alg = 0;
+    for (int32_t i = 0; i < ns; ++i) {
+        SubFactor &F = c->fac[i];
+        const int64_t o = c->sub_ptr[i];
+        // absolute row offsets
+        std::vector<int32_t> rabs(F.rows_host.size());
+        for (size_t q = 0; q < rabs.size(); ++q) rabs[q] = F.rows_host[q] < 0 ? -1 : (int32_t)(o + F.rows_host[q]);
+        cudaFree(F.rowidx);
+        F.rowidx = nullptr;
+        CK(dev_upload(&F.rowidx, rabs.data(), rabs.size()));
+        for (int32_t K = 0; K < (int32_t)F.col0.size(); ++K) {
+            const int32_t nsl = std::max(1, (F.ntiles[K] + tpt - 1) / tpt);
+            nslices[chunk_base[i] + K] = F.ntiles[K] > 0 ? nsl : 0;
+            if (F.parent[K] >= 0) need[chunk_base[i] + F.parent[K]] += nsl;
+            for (int32_t sl = 0; sl < nsl; ++sl) keys.push_back({F.level[K], i, K, sl});
+        }
+        bytes_f += 8.0 * F.panel_doubles + 4.0 * F.rows_host.size();
+        bytes_alg += 8.0 * F.nnz_lower;
+    }
+    auto make_task = [&](const Key &k) {
+        const SubFactor &F = c->fac[k.sub];
+        TriTask t;
+        const int32_t t0 = k.slice * tpt;
+        const int32_t nt = std::max(0, std::min(tpt, F.ntiles[k.chunk] - t0));
+        t.panel = F.panel + F.tile_off[k.chunk] + (int64_t)t0 * 32 * F.w[k.chunk];
+        t.rowidx = F.rowidx + F.row_off[k.chunk] + (int64_t)t0 * 32;
+        t.dinv = F.dinv + F.dinv_off[k.chunk];
+        t.col_abs = (int32_t)(c->sub_ptr[k.sub] + F.col0[k.chunk]);
+        t.chunk = chunk_base[k.sub] + k.chunk;
+        t.parent = F.parent[k.chunk] >= 0 ? chunk_base[k.sub] + F.parent[k.chunk] : -1;
+        t.w = (int16_t)F.w[k.chunk];
+        t.ntiles = (int16_t)nt;
+        t.first = k.slice == 0;
+        t.pad = 0;
+        return t;
+    };
+    std::stable_sort(keys.begin(), keys.end(), [](const Key &a, const Key &b) { return a.level < b.level; });
+    std::vector<TriTask> fwd, bwd;
+    fwd.reserve(keys.size());
+    for (const Key &k : keys) fwd.push_back(make_task(k));
+    for (auto it = keys.rbegin(); it != keys.rend(); ++it) {
+        TriTask t = make_task(*it);
+        if (t.ntiles > 0) bwd.push_back(t);
+    }
+    c->n_fwd = (int32_t)fwd.size();
+    c->n_bwd = (int32_t)bwd.size();
+    CK(dev_upload(&c->fwd_tasks, fwd.data(), fwd.size()));
+    CK(dev_upload(&c->bwd_tasks, bwd.data(), bwd.size()));
+    CK(dev_upload(&c->need, need.data(), need.size()));
+    CK(dev_upload(&c->nslices, nslices.data(), nslices.size()));
+    CU(cudaMalloc((void **)&c->cnt, sizeof(int) * (2 * (size_t)c->nchunks + 2)));
+    int bps_f = 0, bps_b = 0;
+    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps_f, trisolve_fwd_kernel, 256, 0));
+    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps_b, trisolve_bwd_kernel, 256, 0));
+    c->tri_grid = std::max(1, std::min(bps_f, bps_b)) * c->sm_count;
+    if (const char *e = getenv("DDM_TRI_BLOCKS_PER_SM")) c->tri_grid = std::max(1, std::min(atoi(e), std::min(bps_f, bps_b))) * c->sm_count;
+    // algorithmic bytes
+    double zbytes = 0;
+    for (int32_t i = 0; i < ns; ++i) zbytes += 8.0 * c->sub_k[i] * sub_n[i];
+    c->stats["restrict"] = 20.0 * P;
+    c->stats["trisolve_fwd"] = bytes_alg + 16.0 * P;
+    c->stats["trisolve_bwd"] = bytes_alg + 16.0 * P;
+    c->stats["trisolve_stored"] = bytes_f;
+    c->stats["prolong"] = 20.0 * P + 16.0 * c->nloc;
+    c->stats["coarse"] = 2.0 * zbytes + 8.0 * (double)c->N0 * c->N0;
+    c->stats["factor_nnz"] = bytes_alg / 8.0;
+    c->stats["n_tasks_fwd"] = c->n_fwd;
+    c->stats["n_chunks"] = c->nchunks;
+    c->finalized = true;
+    return 0;
+}
+
+// ------------------------------------------------------------------------------------------------ vectors
+extern "C" int ddm_vec_create(ddm_ctx *c, ddm_vec **out)
+{
+    CU(cudaSetDevice(c->device));
+    if (!c->rowptr) return fail("upload the operator before creating vectors");
+    ddm_vec *v = new ddm_vec{c, nullptr};
+    CU(cudaMalloc((void **)&v->d, sizeof(double) * std::max<int64_t>(1, c->nloc)));
+    CU(cudaMemsetAsync(v->d, 0, sizeof(double) * c->nloc, c->s));
+    *out = v;
+    return 0;
+}
+extern "C" int ddm_vec_destroy(ddm_vec *v)
+{
+    if (!v) return 0;
+    cudaFree(v->d);
+    delete v;
+    return 0;
+}
+extern "C" double *ddm_vec_device_ptr(ddm_vec *v) { return v->d; }
+extern "C" int ddm_vec_upload(ddm_vec *v, const double *h)
+{
+    CU(cudaMemcpyAsync(v->d, h, sizeof(double) * v->ctx->n_own, cudaMemcpyHostToDevice, v->ctx->s));
+    CU(cudaStreamSynchronize(v->ctx->s));
+    return 0;
+}
+extern "C" int ddm_vec_download(const ddm_vec *v, double *h)
+{
+    CU(cudaMemcpyAsync(h, v->d, sizeof(double) * v->ctx->n_own, cudaMemcpyDeviceToHost, v->ctx->s));
+    CU(cudaStreamSynchronize(v->ctx->s));
+    return 0;
+}
+extern "C" int ddm_vec_fill(ddm_vec *v, double a)
+{
+    ddm_ctx *c = v->ctx;
+    if (a == 0.0) CU(cudaMemsetAsync(v->d, 0, sizeof(double) * c->nloc, c->s));
+    else LAUNCH(c, fill_kernel, stream_grid(c, c->n_own), 256, c->n_own, a, v->d);
+    return 0;
+}
+extern "C" int ddm_vec_copy(ddm_vec *dst, const ddm_vec *src)
+{
+    CU(cudaMemcpyAsync(dst->d, src->d, sizeof(double) * dst->ctx->n_own, cudaMemcpyDeviceToDevice, dst->ctx->s));
+    return 0;
+}
+extern "C" int ddm_vec_axpy(ddm_vec *y, double a, const ddm_vec *x)
+{
+    ddm_ctx *c = y->ctx;
+    LAUNCH(c, axpy_kernel, stream_grid(c, c->n_own), 256, c->n_own, a, x->d, y->d);
+    return 0;
+}
+extern "C" int ddm_vec_scale(ddm_vec *y, double a)
+{
+    ddm_ctx *c = y->ctx;
+    LAUNCH(c, scale_kernel, stream_grid(c, c->n_own), 256, c->n_own, a, y->d);
+    return 0;
+}
+extern "C" int ddm_vec_add(ddm_vec *y, const ddm_vec *x) { return ddm_vec_axpy(y, 1.0, x); }
+extern "C" int ddm_vec_xpay(ddm_vec *y, double a, const ddm_vec *x)
+{
+    ddm_ctx *c = y->ctx;
+    LAUNCH(c, xpay_kernel, stream_grid(c, c->n_own), 256, c->n_own, a, x->d, y->d);
+    return 0;
+}
+
+// ------------------------------------------------------------------------------------------------ operator, dot
+static int spmv(ddm_ctx *c, double *x, double *y, double alpha, int mode)
+{
+    ScopedTimer tm(c, "Operator/apply");
+    CK(halo_forward(c, x));
+    const int G = c->spmv_group;
+    const int grid = nblocks(c->n_own * G);
+    switch (G) {
+    case 2: LAUNCH(c, spmv_csr_kernel<2>, grid, 256, c->n_own, c->rowptr, c->col, c->val, x, y, alpha, mode); break;
+    case 4: LAUNCH(c, spmv_csr_kernel<4>, grid, 256, c->n_own, c->rowptr, c->col, c->val, x, y, alpha, mode); break;
+    case 8: LAUNCH(c, spmv_csr_kernel<8>, grid, 256, c->n_own, c->rowptr, c->col, c->val, x, y, alpha, mode); break;
+    case 16: LAUNCH(c, spmv_csr_kernel<16>, grid, 256, c->n_own, c->rowptr, c->col, c->val, x, y, alpha, mode); break;
+    default: LAUNCH(c, spmv_csr_kernel<32>, grid, 256, c->n_own, c->rowptr, c->col, c->val, x, y, alpha, mode); break;
+    }
+    return 0;
+}
+extern "C" int ddm_op_apply(ddm_ctx *c, ddm_vec *x, ddm_vec *y) { return spmv(c, x->d, y->d, 1.0, 0); }
+extern "C" int ddm_op_applyscaleadd(ddm_ctx *c, double alpha, ddm_vec *x, ddm_vec *y) { return spmv(c, x->d, y->d, alpha, 1); }
+
+// result lands in c->scal[slot]; with several ranks it is all-reduced there
+static int dot_dev(ddm_ctx *c, const double *x, const double *y, int slot)
+{
+    LAUNCH(c, dot_partial_kernel, c->nred, 256, c->n_own, x, y, c->partial);
+    LAUNCH(c, reduce_final_kernel, 1, 256, c->nred, c->partial, c->scal + slot);
+    if (c->nranks > 1) NC(ncclAllReduce(c->scal + slot, c->scal + slot, 1, ncclDouble, ncclSum, c->comm, c->s));
+    return 0;
+}
+static int fetch_scalar(ddm_ctx *c, int slot, double *out)
+{
+    CU(cudaMemcpyAsync(c->h_scal + slot, c->scal + slot, sizeof(double), cudaMemcpyDeviceToHost, c->s));
+    CU(cudaStreamSynchronize(c->s));
+    *out = c->h_scal[slot];
+    return 0;
+}
+extern "C" int ddm_dot(ddm_ctx *c, const ddm_vec *x, const ddm_vec *y, double *out)
+{
+    CK(dot_dev(c, x->d, y->d, 0));
+    return fetch_scalar(c, 0, out);
+}
+extern "C" int ddm_norm(ddm_ctx *c, const ddm_vec *x, double *out)
+{
+    double v;
+    CK(ddm_dot(c, x, x, &v));
+    *out = std::sqrt(v);
+    return 0;
+}
+
+// ------------------------------------------------------------------------------------------------ preconditioners
+static int need_final(ddm_ctx *c)
+{
+    if (!c->finalized) return fail("call ddm_finalize after the uploads");
+    return 0;
+}
+
+static int restrict_all(ddm_ctx *c, const double *d, int with_coarse)
+{
+    ScopedTimer tm(c, "Schwarz/get defect");
+    LAUNCH(c, restrict_kernel, c->nseg, 256, c->segs, c->gidx, d, c->W, (double *)nullptr, with_coarse, c->zoff, c->d_sub_n,
+           c->d_sub_k, c->Zp, c->cpartial, c->kpad);
+    return 0;
+}
+
+static int coarse_solve(ddm_ctx *c)
+{
+    ScopedTimer tm(c, "GalerkinPrec/coarse solve");
+    const int N0 = c->N0;
+    if (c->nranks > 1) CU(cudaMemsetAsync(c->d0, 0, sizeof(double) * N0, c->s));
+    LAUNCH(c, coarse_restrict_final_kernel, c->nsub, 64, c->nsub, c->seg_ptr, c->d_sub_k, c->d_koff, c->cpartial, c->kpad, c->d0);
+    if (c->nranks > 1) NC(ncclAllReduce(c->d0, c->d0, N0, ncclDouble, ncclSum, c->comm, c->s)); // gatherv (galerkin_preconditioner.hh:171)
+    const int grid = nblocks((int64_t)N0 * 32);
+    // y = A0inv d0, then one refinement step: y += A0inv (d0 - A0 y)
+    LAUNCH(c, dense_gemv_kernel, grid, 256, N0, c->A0inv, c->d0, c->y0, (const double *)nullptr, 1.0);
+    LAUNCH(c, dense_gemv_kernel, grid, 256, N0, c->A0, c->y0, c->r0, c->d0, -1.0);
+    LAUNCH(c, dense_gemv_kernel, grid, 256, N0, c->A0inv, c->r0, c->y0, c->y0, 1.0);
+    return 0;
+}
+
+static int trisolve(ddm_ctx *c)
+{
+    ScopedTimer tm(c, "Schwarz/local solve");
+    CU(cudaMemsetAsync(c->cnt, 0, sizeof(int) * (2 * (size_t)c->nchunks + 2), c->s));
+    int *cnt_f = c->cnt, *cnt_b = c->cnt + c->nchunks, *tick_f = c->cnt + 2 * c->nchunks, *tick_b = tick_f + 1;
+    {
+        void *args[] = {&c->fwd_tasks, &c->n_fwd, &c->W, &c->X, &c->need, &cnt_f, &tick_f};
+        CU(cudaLaunchCooperativeKernel((void *)trisolve_fwd_kernel, dim3(c->tri_grid), dim3(256), args, 0, c->s));
+        c->launches++;
+    }
+    if (c->n_bwd > 0) {
+        void *args[] = {&c->bwd_tasks, &c->n_bwd, &c->X, &c->nslices, &cnt_b, &tick_b};
+        CU(cudaLaunchCooperativeKernel((void *)trisolve_bwd_kernel, dim3(c->tri_grid), dim3(256), args, 0, c->s));
+        c->launches++;
+    }
+    return 0;
+}
+
+// x (+)= sum_i R_i^T ( [pou_i] X_i*fine + Z_i y_i )
+static int prolong(ddm_ctx *c, double *x, int fine, int restricted, int with_coarse, int accumulate)
+{
+    ScopedTimer tm(c, "Schwarz/add solution");
+    const double *pp = (restricted && c->have_pou) ? c->pouP : nullptr;
+    if (!fine || pp || with_coarse)
+        LAUNCH(c, prolong_scale_kernel, c->nseg, 256, c->segs, c->X, pp, fine, with_coarse, c->zoff, c->d_sub_n, c->d_sub_k,
+               c->d_koff, c->Zp, c->y0);
+    if (c->nranks > 1 && accumulate) {
+        // keep the owned accumulation local: sum into a scratch vector, exchange, then add
+        double *t = c->tmp[3]->d;
+        LAUNCH(c, gather_sum_kernel, nblocks(c->nloc), 256, c->nloc, c->dptr, c->dpos, c->X, t, 0);
+        CK(halo_reverse_add(c, t));
+        LAUNCH(c, axpy_kernel, stream_grid(c, c->n_own), 256, c->n_own, 1.0, t, x);
+        return 0;
+    }
+    LAUNCH(c, gather_sum_kernel, nblocks(c->nloc), 256, c->nloc, c->dptr, c->dpos, c->X, x, accumulate);
+    CK(halo_reverse_add(c, x));
+    return 0;
+}
+
+extern "C" int ddm_schwarz_apply(ddm_ctx *c, int type, ddm_vec *d, ddm_vec *x)
+{
+    CK(need_final(c));
+    ScopedTimer tm(c, "Schwarz/apply");
+    CK(halo_forward(c, d->d));
+    CK(restrict_all(c, d->d, 0));
+    CK(trisolve(c));
+    return prolong(c, x->d, 1, type == DDM_SCHWARZ_RESTRICTED, 0, 0);
+}
+
+extern "C" int ddm_coarse_apply(ddm_ctx *c, ddm_vec *d, ddm_vec *x)
+{
+    CK(need_final(c));
+    if (c->N0 <= 0) return fail("no coarse space uploaded");
+    ScopedTimer tm(c, "GalerkinPrec/apply");
+    CK(halo_forward(c, d->d));
+    CK(restrict_all(c, d->d, 1));
+    CK(coarse_solve(c));
+    return prolong(c, x->d, 0, 0, 1, 0);
+}
+
+extern "C" int ddm_twolevel_apply(ddm_ctx *c, int type, int mode, int with_coarse, ddm_vec *d, ddm_vec *x)
+{
+    CK(need_final(c));
+    if (with_coarse && c->N0 <= 0) return fail("no coarse space uploaded");
+    ScopedTimer tm(c, "CombinedPreconditioner/apply");
+    const int restricted = type == DDM_SCHWARZ_RESTRICTED;
+    CK(halo_forward(c, d->d));
+    if (!with_coarse) {
+        CK(restrict_all(c, d->d, 0));
+        CK(trisolve(c));
+        return prolong(c, x->d, 1, restricted, 0, 0);
+    }
+    if (mode == DDM_COMBINE_ADDITIVE) {
+        // one restriction and one prolongation serve both levels (the reference does each twice)
+        CK(restrict_all(c, d->d, 1));
+        CK(coarse_solve(c));
+        CK(trisolve(c));
+        return prolong(c, x->d, 1, restricted, 1, 0);
+    }
+    // multiplicative: x = M1 d;  x += M0 (d - A x)   (combined_preconditioner.hh:144-158)
+    CK(restrict_all(c, d->d, 0));
+    CK(trisolve(c));
+    CK(prolong(c, x->d, 1, restricted, 0, 0));
+    double *dn = c->tmp[2]->d;
+    CU(cudaMemcpyAsync(dn, d->d, sizeof(double) * c->n_own, cudaMemcpyDeviceToDevice, c->s));
+    CK(spmv(c, x->d, dn, -1.0, 1));
+    CK(halo_forward(c, dn));
+    CK(restrict_all(c, dn, 1));
+    CK(coarse_solve(c));
+    return prolong(c, x->d, 0, 0, 1, 1);
+}
+
+// ------------------------------------------------------------------------------------------------ PCG
+extern "C" int ddm_pcg_solve(ddm_ctx *c, ddm_vec *b, ddm_vec *x, double reduction, int32_t maxit, int type, int mode,
+                             int with_coarse, ddm_result *res, double *history)
+{
+    CK(need_final(c));
+    ddm_vec *p = c->tmp[0], *q = c->tmp[1];
+    cudaEvent_t e0, e1;
+    CU(cudaEventCreate(&e0));
+    CU(cudaEventCreate(&e1));
+    CU(cudaEventRecord(e0, c->s));
+    // scal slots: 0 scratch, 1 alpha, 2 def^2, 3/4 rho (alternating)
+    CK(spmv(c, x->d, b->d, -1.0, 1)); // b <- b - A x
+    CK(dot_dev(c, b->d, b->d, 2));
+    double def2;
+    CK(fetch_scalar(c, 2, &def2));
+    double def = std::sqrt(def2), def0 = def;
+    if (history) history[0] = def;
+    if (!std::isfinite(def)) return fail("CG: defect is infinite or NaN");
+    int i = 0;
+    bool conv = (def < def0 * reduction || def < 1e-30);
+    if (!conv) {
+        CK(ddm_vec_fill(p, 0.0));
+        CK(ddm_twolevel_apply(c, type, mode, with_coarse, b, p));
+        int cur = 3;
+        CK(dot_dev(c, p->d, b->d, cur)); // rholast
+        for (i = 1; i <= maxit; ++i) {
+            CK(spmv(c, p->d, q->d, 1.0, 0));
+            CK(dot_dev(c, p->d, q->d, 1));
+            LAUNCH(c, cg_update_kernel, c->nred, 256, c->n_own, c->scal + cur, c->scal + 1, def == 0.0 ? 1 : 0, p->d, q->d, x->d,
+                   b->d, c->partial);
+            LAUNCH(c, reduce_final_kernel, 1, 256, c->nred, c->partial, c->scal + 2);
+            if (c->nranks > 1) NC(ncclAllReduce(c->scal + 2, c->scal + 2, 1, ncclDouble, ncclSum, c->comm, c->s));
+            CK(fetch_scalar(c, 2, &def2));
+            def = std::sqrt(def2);
+            if (history) history[i] = def;
+            if (!std::isfinite(def)) return fail("CG: defect is infinite or NaN at iteration %d", i);
+            conv = (def < def0 * reduction || def < 1e-30);
+            if (conv) break;
+            CK(ddm_twolevel_apply(c, type, mode, with_coarse, b, q));
+            const int nxt = cur == 3 ? 4 : 3;
+            CK(dot_dev(c, q->d, b->d, nxt));
+            LAUNCH(c, xpay_dev_kernel, stream_grid(c, c->n_own), 256, c->n_own, c->scal + nxt, c->scal + cur, def == 0.0 ? 1 : 0,
+                   q->d, p->d);
+            cur = nxt;
+        }
+        if (i > maxit) i = maxit;
+    }
+    CU(cudaEventRecord(e1, c->s));
+    CU(cudaEventSynchronize(e1));
+    float ms = 0;
+    CU(cudaEventElapsedTime(&ms, e0, e1));
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    if (res) {
+        res->iterations = i;
+        res->converged = conv ? 1 : 0;
+        res->reduction = def0 > 0 ? def / def0 : 0.0;
+        res->conv_rate = i > 0 ? std::pow(res->reduction, 1.0 / i) : 0.0;
+        res->elapsed = ms * 1e-3;
+        res->def0 = def0;
+    }
+    return 0;
+}
+
+// ------------------------------------------------------------------------------------------------ host-pointer forms
+static int stage_in(ddm_ctx *c, ddm_vec *v, const double *h, int slot)
+{
+    double *st = c->h_stage + (int64_t)slot * c->n_own;
+    memcpy(st, h, sizeof(double) * c->n_own);
+    CU(cudaMemcpyAsync(v->d, st, sizeof(double) * c->n_own, cudaMemcpyHostToDevice, c->s));
+    return 0;
+}
+static int stage_out(ddm_ctx *c, const ddm_vec *v, double *h, int slot)
+{
+    double *st = c->h_stage + (int64_t)slot * c->n_own;
+    CU(cudaMemcpyAsync(st, v->d, sizeof(double) * c->n_own, cudaMemcpyDeviceToHost, c->s));
+    CU(cudaStreamSynchronize(c->s));
+    memcpy(h, st, sizeof(double) * c->n_own);
+    return 0;
+}
+extern "C" int ddm_op_apply_host(ddm_ctx *c, const double *x, double *y)
+{
+    CK(need_final(c));
+    CK(stage_in(c, c->hv[0], x, 0));
+    CK(ddm_op_apply(c, c->hv[0], c->hv[1]));
+    return stage_out(c, c->hv[1], y, 1);
+}
+extern "C" int ddm_op_applyscaleadd_host(ddm_ctx *c, double alpha, const double *x, double *y)
+{
+    CK(need_final(c));
+    CK(stage_in(c, c->hv[0], x, 0));
+    CK(stage_in(c, c->hv[1], y, 1));
+    CK(ddm_op_applyscaleadd(c, alpha, c->hv[0], c->hv[1]));
+    return stage_out(c, c->hv[1], y, 1);
+}
+extern "C" int ddm_dot_host(ddm_ctx *c, const double *x, const double *y, double *out)
+{
+    CK(need_final(c));
+    CK(stage_in(c, c->hv[0], x, 0));
+    if (y != x) CK(stage_in(c, c->hv[1], y, 1));
+    return ddm_dot(c, c->hv[0], y != x ? c->hv[1] : c->hv[0], out);
+}
+extern "C" int ddm_twolevel_apply_host(ddm_ctx *c, int type, int mode, int with_coarse, const double *d, double *x)
+{
+    CK(need_final(c));
+    CK(stage_in(c, c->hv[0], d, 0));
+    CK(ddm_twolevel_apply(c, type, mode, with_coarse, c->hv[0], c->hv[1]));
+    return stage_out(c, c->hv[1], x, 1);
+}
+extern "C" int ddm_pcg_solve_host(ddm_ctx *c, double *b, double *x, double reduction, int32_t maxit, int type, int mode,
+                                  int with_coarse, ddm_result *res, double *history)
+{
+    CK(need_final(c));
+    CK(stage_in(c, c->hv[0], b, 0));
+    CK(stage_in(c, c->hv[1], x, 1));
+    CK(ddm_pcg_solve(c, c->hv[0], c->hv[1], reduction, maxit, type, mode, with_coarse, res, history));
+    CK(stage_out(c, c->hv[0], b, 0));
+    return stage_out(c, c->hv[1], x, 1);
+}
+
+// ------------------------------------------------------------------------------------------------ introspection
+extern "C" int ddm_get_stat(ddm_ctx *c, const char *key, double *value)
+{
+    auto it = c->stats.find(key);
+    if (it == c->stats.end()) return fail("unknown stat '%s'", key);
+    *value = it->second;
+    return 0;
+}
+extern "C" int ddm_timers_enable(ddm_ctx *c, int on)
+{
+    c->timers_on = on != 0;
+    return 0;
+}
+static void drain_timers(ddm_ctx *c)
+{
+    cudaStreamSynchronize(c->s);
+    for (auto &r : c->trecs) {
+        float ms = 0;
+        cudaEventElapsedTime(&ms, r.a, r.b);
+        auto &acc = c->tacc[r.name];
+        acc.first += ms;
+        acc.second += 1;
+        cudaEventDestroy(r.a);
+        cudaEventDestroy(r.b);
+    }
+    c->trecs.clear();
+}
+extern "C" int ddm_timers_reset(ddm_ctx *c)
+{
+    drain_timers(c);
+    c->tacc.clear();
+    return 0;
+}
+extern "C" int ddm_get_timer(ddm_ctx *c, const char *event, double *total_ms, int64_t *calls)
+{
+    drain_timers(c);
+    auto it = c->tacc.find(event);
+    if (it == c->tacc.end()) {
+        *total_ms = 0;
+        *calls = 0;
+        return 0;
+    }
+    *total_ms = it->second.first;
+    *calls = it->second.second;
+    return 0;
+}
+extern "C" int64_t ddm_kernel_launches(ddm_ctx *c) { return c->launches; }
+extern "C" int ddm_sync(ddm_ctx *c)
+{
+    CU(cudaStreamSynchronize(c->s));
+    CU(cudaGetLastError());
+    return 0;
+}

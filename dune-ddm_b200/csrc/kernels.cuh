@@ -1,0 +1,458 @@
+// Device kernels of the solve phase (sm_100a).  Every kernel here is HBM-bandwidth bound; the
+// layouts are chosen so that each warp-wide access is a contiguous 256-byte (or wider) segment.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace ddm {
+
+constexpr int kWarp = 32;
+constexpr unsigned kFull = 0xffffffffu;
+
+// ------------------------------------------------------------------------------------------------
+// K1  CSR SpMV, scalar FP64.  Replaces BCRSMatrix::mv / usmv
+// (extern/dune-istl/dune/istl/bcrsmatrix.hh:1641-1661, 1713-1730).
+// G lanes cooperate on one row (G chosen from the mean row length at upload); the G-lane groups of
+// a warp read neighbouring rows, so value/column streams stay contiguous across the warp.
+// mode 0: y = A x      mode 1: y += alpha * A x
+// ------------------------------------------------------------------------------------------------
+template <int G>
+__global__ void __launch_bounds__(256) spmv_csr_kernel(int64_t n, const int32_t *__restrict__ rowptr,
+                                                       const int32_t *__restrict__ col,
+                                                       const double *__restrict__ val,
+                                                       const double *__restrict__ x, double *__restrict__ y,
+                                                       double alpha, int mode)
+{
+    const int64_t gtid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t row = gtid / G;
+    const int lane = (int)(gtid % G);
+    double acc = 0.0;
+    if (row < n) {
+        const int32_t b = rowptr[row], e = rowptr[row + 1];
+        for (int32_t k = b + lane; k < e; k += G) acc = fma(val[k], __ldg(x + col[k]), acc);
+    }
+#pragma unroll
+    for (int o = G / 2; o > 0; o >>= 1) acc += __shfl_xor_sync(kFull, acc, o, G);
+    if (row < n && lane == 0) {
+        if (mode == 0) y[row] = acc;
+        else y[row] += alpha * acc;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// K8/K9  vector updates and deterministic two-stage reductions (Krylov recurrences of
+// extern/dune-istl/dune/istl/solvers.hh:312-335; masked dot of owneroverlapcopy.hh:398-444).
+// ------------------------------------------------------------------------------------------------
+__global__ void axpy_kernel(int64_t n, double a, const double *__restrict__ x, double *__restrict__ y)
+{
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+        y[i] = fma(a, x[i], y[i]);
+}
+__global__ void scale_kernel(int64_t n, double a, double *__restrict__ y)
+{
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+        y[i] *= a;
+}
+__global__ void fill_kernel(int64_t n, double a, double *__restrict__ y)
+{
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+        y[i] = a;
+}
+// y = x + a*y
+__global__ void xpay_kernel(int64_t n, double a, const double *__restrict__ x, double *__restrict__ y)
+{
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+        y[i] = fma(a, y[i], x[i]);
+}
+// y = x + (num/den)*y with the scalars on the device (p = q + beta p, beta = rho / rholast)
+__global__ void xpay_dev_kernel(int64_t n, const double *__restrict__ num, const double *__restrict__ den, int zero,
+                                const double *__restrict__ x, double *__restrict__ y)
+{
+    const double a = zero ? 0.0 : (*num) / (*den);
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+        y[i] = fma(a, y[i], x[i]);
+}
+
+__device__ __forceinline__ double block_sum_256(double v, double *sm)
+{
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(kFull, v, o);
+    const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
+    if (l == 0) sm[w] = v;
+    __syncthreads();
+    double t = 0.0;
+    if (w == 0) {
+        t = (l < (int)(blockDim.x >> 5)) ? sm[l] : 0.0;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(kFull, t, o);
+    }
+    __syncthreads();
+    return t; // valid in thread 0
+}
+
+// stage 1: per-block partial of sum x*y (fixed grid => fixed summation tree => reproducible)
+__global__ void __launch_bounds__(256) dot_partial_kernel(int64_t n, const double *__restrict__ x,
+                                                          const double *__restrict__ y, double *__restrict__ partial)
+{
+    __shared__ double sm[8];
+    double acc = 0.0;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+        acc = fma(x[i], y[i], acc);
+    const double t = block_sum_256(acc, sm);
+    if (threadIdx.x == 0) partial[blockIdx.x] = t;
+}
+// stage 2: one block sums the partials in a fixed order
+__global__ void __launch_bounds__(256) reduce_final_kernel(int np, const double *__restrict__ partial,
+                                                           double *__restrict__ out)
+{
+    __shared__ double sm[8];
+    double acc = 0.0;
+    for (int i = threadIdx.x; i < np; i += blockDim.x) acc += partial[i];
+    const double t = block_sum_256(acc, sm);
+    if (threadIdx.x == 0) *out = t;
+}
+// fused CG update (solvers.hh:318-322): lambda = rholast/alpha; x += lambda p; r -= lambda q; partial |r|^2
+__global__ void __launch_bounds__(256) cg_update_kernel(int64_t n, const double *__restrict__ rholast,
+                                                        const double *__restrict__ alpha, int zero,
+                                                        const double *__restrict__ p, const double *__restrict__ q,
+                                                        double *__restrict__ x, double *__restrict__ r,
+                                                        double *__restrict__ partial)
+{
+    __shared__ double sm[8];
+    const double lambda = zero ? 0.0 : (*rholast) / (*alpha);
+    double acc = 0.0;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        x[i] = fma(lambda, p[i], x[i]);
+        const double ri = fma(-lambda, q[i], r[i]);
+        r[i] = ri;
+        acc = fma(ri, ri, acc);
+    }
+    const double t = block_sum_256(acc, sm);
+    if (threadIdx.x == 0) partial[blockIdx.x] = t;
+}
+
+// ------------------------------------------------------------------------------------------------
+// K2 + K5  restriction of the defect to all hosted subdomains, fused with the coarse restriction.
+// schwarz.hh:121-125 / galerkin_preconditioner.hh:159-167: W[p] = d[gidx[p]] (pivot order), and for the
+// segment's subdomain the partial sums  sum_p Z[p,k] d_p  for its k basis vectors.
+// One block per segment (<= kSeg consecutive positions of one subdomain).
+// ------------------------------------------------------------------------------------------------
+constexpr int kSeg = 2048;
+constexpr int kKmax = 16; // basis vectors handled per pass
+
+struct Segment {
+    int32_t sub;      // hosted subdomain
+    int32_t start;    // first position (absolute offset into W)
+    int32_t len;      // number of positions
+    int32_t local0;   // start - base of the subdomain
+};
+
+__global__ void __launch_bounds__(256) restrict_kernel(const Segment *__restrict__ segs, const int32_t *__restrict__ gidx,
+                                                       const double *__restrict__ d, double *__restrict__ W,
+                                                       double *__restrict__ W2, int with_coarse,
+                                                       const int64_t *__restrict__ zoff, const int32_t *__restrict__ sub_n,
+                                                       const int32_t *__restrict__ sub_k, const double *__restrict__ Zp,
+                                                       double *__restrict__ partial /* [nseg][kpad] */, int kpad)
+{
+    __shared__ double sm[8];
+    const Segment sg = segs[blockIdx.x];
+    const int k = with_coarse ? sub_k[sg.sub] : 0;
+    const int32_t ni = sub_n[sg.sub];
+    const double *Zi = with_coarse ? Zp + zoff[sg.sub] + sg.local0 : nullptr;
+    for (int k0 = 0; k0 < (k > 0 ? k : 1); k0 += kKmax) {
+        double acc[kKmax];
+#pragma unroll
+        for (int j = 0; j < kKmax; ++j) acc[j] = 0.0;
+        for (int t = threadIdx.x; t < sg.len; t += blockDim.x) {
+            const int p = sg.start + t;
+            const double v = __ldg(d + gidx[p]);
+            if (k0 == 0) {
+                W[p] = v;
+                if (W2) W2[p] = 0.0;
+            }
+#pragma unroll
+            for (int j = 0; j < kKmax; ++j)
+                if (k0 + j < k) acc[j] = fma(Zi[(int64_t)(k0 + j) * ni + t], v, acc[j]);
+        }
+        if (k > 0) {
+#pragma unroll
+            for (int j = 0; j < kKmax; ++j) {
+                if (k0 + j < k) { // uniform across the block
+                    const double s = block_sum_256(acc[j], sm);
+                    if (threadIdx.x == 0) partial[(int64_t)blockIdx.x * kpad + k0 + j] = s;
+                }
+            }
+        }
+    }
+}
+
+// second stage of K5: d0[koff[i]+k] = sum over the segments of subdomain i, in segment order
+__global__ void coarse_restrict_final_kernel(int nsub, const int32_t *__restrict__ seg_ptr, const int32_t *__restrict__ sub_k,
+                                             const int32_t *__restrict__ koff, const double *__restrict__ partial, int kpad,
+                                             double *__restrict__ d0)
+{
+    const int i = blockIdx.x;
+    if (i >= nsub) return;
+    for (int k = threadIdx.x; k < sub_k[i]; k += blockDim.x) {
+        double acc = 0.0;
+        for (int s = seg_ptr[i]; s < seg_ptr[i + 1]; ++s) acc += partial[(int64_t)s * kpad + k];
+        d0[koff[i] + k] = acc;
+    }
+}
+
+// K6  dense coarse solve as matrix-vector products with the explicit inverse (plus one refinement step
+// driven from the host side): out = M v, M row-major N x N, one warp per row.
+__global__ void __launch_bounds__(256) dense_gemv_kernel(int N, const double *__restrict__ M, const double *__restrict__ v,
+                                                         double *out, const double *addto, double sign)
+{
+    const int row = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    if (row >= N) return;
+    const double *Mr = M + (int64_t)row * N;
+    double acc = 0.0;
+    for (int j = lane; j < N; j += 32) acc = fma(Mr[j], __ldg(v + j), acc);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(kFull, acc, o);
+    if (lane == 0) out[row] = addto ? addto[row] + sign * acc : sign * acc;
+}
+
+// ------------------------------------------------------------------------------------------------
+// K4 + K7  prolongation.  Stage a (position-wise, coalesced):
+//   X[p] <- (pou ? pou[p] : 1) * X[p] * fine  +  sum_k Z[p,k] y[koff+k]
+// (schwarz.hh:139-141 and galerkin_preconditioner.hh:186-188), stage b (DOF-wise gather, no atomics,
+// fixed order): x[v] (+)= sum over the positions that map to v  (the halo sums of schwarz.hh:138/142
+// and galerkin_preconditioner.hh:190 for all subdomains hosted on this GPU).
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) prolong_scale_kernel(const Segment *__restrict__ segs, double *__restrict__ X,
+                                                            const double *__restrict__ pouP, int fine, int with_coarse,
+                                                            const int64_t *__restrict__ zoff, const int32_t *__restrict__ sub_n,
+                                                            const int32_t *__restrict__ sub_k, const int32_t *__restrict__ koff,
+                                                            const double *__restrict__ Zp, const double *__restrict__ y0)
+{
+    __shared__ double ys[64];
+    const Segment sg = segs[blockIdx.x];
+    const int k = with_coarse ? sub_k[sg.sub] : 0;
+    const int32_t ni = sub_n[sg.sub];
+    const double *Zi = with_coarse ? Zp + zoff[sg.sub] + sg.local0 : nullptr;
+    for (int t = threadIdx.x; t < sg.len; t += blockDim.x) {
+        const int p = sg.start + t;
+        double v = 0.0;
+        if (fine) v = pouP ? pouP[p] * X[p] : X[p];
+        X[p] = v;
+    }
+    for (int k0 = 0; k0 < k; k0 += 64) {
+        __syncthreads();
+        if (threadIdx.x < 64 && k0 + threadIdx.x < k) ys[threadIdx.x] = y0[koff[sg.sub] + k0 + threadIdx.x];
+        __syncthreads();
+        const int kk = min(64, k - k0);
+        for (int t = threadIdx.x; t < sg.len; t += blockDim.x) {
+            double v = X[sg.start + t];
+            for (int j = 0; j < kk; ++j) v = fma(Zi[(int64_t)(k0 + j) * ni + t], ys[j], v);
+            X[sg.start + t] = v;
+        }
+    }
+}
+
+__global__ void __launch_bounds__(256) gather_sum_kernel(int64_t nloc, const int32_t *__restrict__ dptr,
+                                                         const int32_t *__restrict__ dpos, const double *__restrict__ X,
+                                                         double *__restrict__ x, int accumulate)
+{
+    const int64_t v = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (v >= nloc) return;
+    double acc = 0.0;
+    for (int32_t q = dptr[v]; q < dptr[v + 1]; ++q) acc += X[dpos[q]];
+    x[v] = accumulate ? x[v] + acc : acc;
+}
+
+// ------------------------------------------------------------------------------------------------
+// K3  batched subdomain solves  x_i = A_i^{-1} d_i  for all hosted subdomains in two persistent kernels.
+//
+// Replaces Dune::Cholmod::apply -> cholmod_l_solve (extern/dune-istl/dune/istl/cholmod.hh:263-306).
+// At upload the supernodal LL^T factor is re-expressed as a block LDL^T with column chunks of width
+// w <= 32:  A = Lt D Lt^T, Lt unit block lower triangular (Lt_below = L_below L_KK^{-1}) and
+// D_K = L_KK L_KK^T stored as its explicit inverse.  With that form no triangular solve is left:
+//   forward : for chunk K in tree order   y_below -= Lt_below y_K          (scatter, RED.F64)
+//   diagonal: z_K = Dinv_K y_K                                              (fused into forward)
+//   backward: for chunk K in reverse      x_K = z_K - Lt_below^T x_below    (gather + warp transpose-reduce)
+// The panels are stored as tiles of 32 rows x w columns, column-major inside the tile, so lane i of a
+// warp owns row i and every load instruction reads 256 contiguous bytes.  Work is cut into tasks
+// (a chunk's run of <= tpt tiles) listed in elimination-tree level order over ALL subdomains; warps
+// take tasks from a ticket counter and synchronise point-to-point through per-chunk counters
+// (a task waits only for tasks with smaller ticket numbers, so the persistent grid cannot deadlock
+// as long as it is co-resident -- it is launched cooperatively).
+// ------------------------------------------------------------------------------------------------
+struct TriTask {
+    const double *panel;   // first tile of the task
+    const int32_t *rowidx; // row offsets into W/X for the task's tiles (-1 = padding)
+    const double *dinv;    // chunk's w x w inverse diagonal block (column-major)
+    int32_t col_abs;       // offset of the chunk's first column in W/X
+    int32_t chunk;         // global chunk id
+    int32_t parent;        // global chunk id of the parent chunk, -1 for a root
+    int16_t w;
+    int16_t ntiles;
+    int32_t first;         // 1 if this task is the first slice of its chunk (does the diagonal step)
+    int32_t pad;
+};
+
+__device__ __forceinline__ int ld_acquire(const int *p)
+{
+    int v;
+    asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+
+__device__ __forceinline__ void wait_counter(const int *cnt, int need, int lane)
+{
+    if (need > 0) {
+        if (lane == 0) {
+            while (ld_acquire(cnt) < need) __nanosleep(40);
+        }
+        __syncwarp();
+    }
+}
+
+// Loads one half-tile (16 columns x 32 rows): 16 independent 256-byte warp loads.
+__device__ __forceinline__ void load_half(double (&pv)[16], const double *P, int w, int h, int lane)
+{
+#pragma unroll
+    for (int j = 0; j < 16; ++j) pv[j] = (h * 16 + j < w) ? __ldcs(P + (h * 16 + j) * 32 + lane) : 0.0;
+}
+
+__global__ void __launch_bounds__(256, 2) trisolve_fwd_kernel(const TriTask *__restrict__ tasks, int ntasks, double *W,
+                                                              double *X, const int32_t *__restrict__ need, int *cnt,
+                                                              int *ticket)
+{
+    const int lane = threadIdx.x & 31;
+    for (;;) {
+        int t = 0;
+        if (lane == 0) t = atomicAdd(ticket, 1);
+        t = __shfl_sync(kFull, t, 0);
+        if (t >= ntasks) break;
+        const TriTask tk = tasks[t];
+        const int w = tk.w;
+        const int nh = tk.ntiles * 2; // half-tiles
+        // the first half-tile is fetched before the dependency wait: its latency overlaps the wait
+        double pv[16];
+        if (nh > 0) load_half(pv, tk.panel, w, 0, lane);
+        wait_counter(cnt + tk.chunk, need[tk.chunk], lane);
+        const double yl = (lane < w) ? __ldcg(W + tk.col_abs + lane) : 0.0;
+        double yv[32];
+#pragma unroll
+        for (int j = 0; j < 32; ++j) yv[j] = __shfl_sync(kFull, yl, j);
+        if (tk.first) {
+            double z = 0.0;
+#pragma unroll
+            for (int j = 0; j < 32; ++j)
+                if (j < w && lane < w) z = fma(__ldg(tk.dinv + j * w + lane), yv[j], z);
+            if (lane < w) X[tk.col_abs + lane] = z;
+        }
+        double acc = 0.0;
+        for (int hh = 0; hh < nh; ++hh) {
+            if (hh & 1) {
+#pragma unroll
+                for (int j = 0; j < 16; ++j) acc = fma(pv[j], yv[16 + j], acc);
+            } else {
+#pragma unroll
+                for (int j = 0; j < 16; ++j) acc = fma(pv[j], yv[j], acc);
+            }
+            if (hh + 1 < nh) load_half(pv, tk.panel + (int64_t)((hh + 1) >> 1) * 32 * w, w, (hh + 1) & 1, lane);
+            if (hh & 1) {
+                const int r = __ldg(tk.rowidx + (hh >> 1) * 32 + lane);
+                if (r >= 0) atomicAdd(W + r, -acc);
+                acc = 0.0;
+            }
+        }
+        __threadfence();
+        __syncwarp();
+        if (lane == 0 && tk.parent >= 0) atomicAdd(cnt + tk.parent, 1);
+    }
+}
+
+__global__ void __launch_bounds__(256, 2) trisolve_bwd_kernel(const TriTask *__restrict__ tasks, int ntasks, double *X,
+                                                              const int32_t *__restrict__ nslices, int *cnt, int *ticket)
+{
+    const int lane = threadIdx.x & 31;
+    for (;;) {
+        int t = 0;
+        if (lane == 0) t = atomicAdd(ticket, 1);
+        t = __shfl_sync(kFull, t, 0);
+        if (t >= ntasks) break;
+        const TriTask tk = tasks[t];
+        const int w = tk.w;
+        const int nh = tk.ntiles * 2;
+        double pv[16];
+        load_half(pv, tk.panel, w, 0, lane);
+        int r = __ldg(tk.rowidx + lane);
+        if (tk.parent >= 0) wait_counter(cnt + tk.parent, nslices[tk.parent], lane);
+        double acc[32];
+#pragma unroll
+        for (int j = 0; j < 32; ++j) acc[j] = 0.0;
+        double xr = (r >= 0) ? __ldcg(X + r) : 0.0;
+        for (int hh = 0; hh < nh; ++hh) {
+            if (hh & 1) {
+#pragma unroll
+                for (int j = 0; j < 16; ++j) acc[16 + j] = fma(pv[j], xr, acc[16 + j]);
+            } else {
+#pragma unroll
+                for (int j = 0; j < 16; ++j) acc[j] = fma(pv[j], xr, acc[j]);
+            }
+            if (hh + 1 < nh) {
+                load_half(pv, tk.panel + (int64_t)((hh + 1) >> 1) * 32 * w, w, (hh + 1) & 1, lane);
+                if (hh & 1) {
+                    r = __ldg(tk.rowidx + ((hh + 1) >> 1) * 32 + lane);
+                    xr = (r >= 0) ? __ldcg(X + r) : 0.0;
+                }
+            }
+        }
+        // transpose-reduce: afterwards lane L holds sum over lanes of acc[L]
+#pragma unroll
+        for (int half = 16; half >= 1; half >>= 1) {
+            const bool upper = (lane & half) != 0;
+#pragma unroll
+            for (int k = 0; k < half; ++k) {
+                const double send = upper ? acc[k] : acc[k + half];
+                const double keep = upper ? acc[k + half] : acc[k];
+                acc[k] = keep + __shfl_xor_sync(kFull, send, half);
+            }
+        }
+        if (lane < w) atomicAdd(X + tk.col_abs + lane, -acc[0]);
+        __threadfence();
+        __syncwarp();
+        if (lane == 0) atomicAdd(cnt + tk.chunk, 1);
+    }
+}
+
+// Setup-time conversion of raw supernodal panels (cholmod layout) into Lt tiles: one warp per tile.
+struct ConvTile {
+    int64_t src;    // offset in raw x of element (first row of tile, first column of chunk)
+    int64_t dst;    // offset in the tile array
+    int64_t linv;   // offset of the chunk's L_KK^{-1} (w x w, column-major, lower)
+    int32_t ld;     // leading dimension (rows) of the raw panel
+    int32_t nrows;  // valid rows in this tile (<= 32)
+    int32_t w;
+    int32_t pad;
+};
+
+__global__ void __launch_bounds__(256) convert_tiles_kernel(int64_t ntiles, const ConvTile *__restrict__ tiles,
+                                                            const double *__restrict__ raw, const double *__restrict__ linv,
+                                                            double *__restrict__ out)
+{
+    const int64_t t = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    if (t >= ntiles) return;
+    const ConvTile ct = tiles[t];
+    const int w = ct.w;
+    double p[32];
+#pragma unroll
+    for (int k = 0; k < 32; ++k) p[k] = (k < w && lane < ct.nrows) ? raw[ct.src + (int64_t)k * ct.ld + lane] : 0.0;
+    const double *Li = linv + ct.linv;
+    for (int j = 0; j < w; ++j) {
+        double acc = 0.0;
+#pragma unroll
+        for (int k = 0; k < 32; ++k)
+            if (k >= j && k < w) acc = fma(p[k], __ldg(Li + (int64_t)j * w + k), acc);
+        out[ct.dst + (int64_t)j * 32 + lane] = acc;
+    }
+}
+
+} // namespace ddm

@@ -1,0 +1,369 @@
+"""Host-side mirror of the reference's solve-phase interfaces over the C ABI.
+
+Class names, argument meaning and error behaviour follow the reference:
+  NonOverlappingOperator / NonOverlappingScalarProduct  (dune/ddm/nonoverlapping_operator.hh:12-96)
+  SchwarzPreconditioner                                  (dune/ddm/schwarz.hh:55-220)
+  GalerkinPreconditioner                                 (dune/ddm/galerkin_preconditioner.hh:48-363)
+  CombinedPreconditioner                                 (dune/ddm/combined_preconditioner.hh:41-180)
+  CGSolver (drop-in loop)                                (extern/dune-istl/dune/istl/solvers.hh:279-340)
+All arithmetic runs in libddm_b200.so on the GPU; this module only moves pointers.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+
+from . import lib as _l
+from .lib import DDMError, Result, check
+from .partition import shard
+
+STANDARD, RESTRICTED = 0, 1
+ADDITIVE, MULTIPLICATIVE = 0, 1
+
+
+def _p(a, t):
+    return a.ctypes.data_as(C.POINTER(t))
+
+
+class DeviceVector:
+    """The vector type X the Krylov loops work on (BlockVector<FieldVector<double,1>> on the device)."""
+
+    def __init__(self, ctx, values=None):
+        self.ctx = ctx
+        self.h = C.c_void_p()
+        check(ctx.lib.ddm_vec_create(ctx.h, C.byref(self.h)))
+        if values is not None:
+            self.upload(values)
+
+    def upload(self, values):
+        v = np.ascontiguousarray(values, dtype=np.float64)
+        if v.size != self.ctx.n_own:
+            raise DDMError(f"vector has {v.size} entries, context owns {self.ctx.n_own}")
+        check(self.ctx.lib.ddm_vec_upload(self.h, _p(v, C.c_double)))
+        return self
+
+    def download(self):
+        out = np.empty(self.ctx.n_own)
+        check(self.ctx.lib.ddm_vec_download(self.h, _p(out, C.c_double)))
+        return out
+
+    def fill(self, a):
+        check(self.ctx.lib.ddm_vec_fill(self.h, C.c_double(a)))
+        return self
+
+    def assign(self, other):
+        check(self.ctx.lib.ddm_vec_copy(self.h, other.h))
+        return self
+
+    def axpy(self, a, x):
+        check(self.ctx.lib.ddm_vec_axpy(self.h, C.c_double(a), x.h))
+        return self
+
+    def __imul__(self, a):
+        check(self.ctx.lib.ddm_vec_scale(self.h, C.c_double(a)))
+        return self
+
+    def __iadd__(self, x):
+        check(self.ctx.lib.ddm_vec_add(self.h, x.h))
+        return self
+
+    def __del__(self):
+        try:
+            if self.h and self.ctx.h:
+                self.ctx.lib.ddm_vec_destroy(self.h)
+        except Exception:
+            pass
+
+
+class Context:
+    """One GPU's share of a two-level Schwarz solve (one ddm_ctx)."""
+
+    def __init__(self, device=0):
+        self.lib = _l.load()
+        self.h = C.c_void_p()
+        check(self.lib.ddm_ctx_create(C.c_int(device), C.byref(self.h)))
+        self.n_own = 0
+        self.shard = None
+        self.world = 1
+
+    @classmethod
+    def from_products(cls, P, device=0, rank=0, world=1, unique_id=None, with_coarse=True):
+        """Upload the setup products (whole problem, or this rank's shard)."""
+        self = cls(device)
+        S = shard(P, rank, world)
+        self.shard, self.world, self.rank = S, world, rank
+        lib = self.lib
+        if world > 1:
+            uid = (C.c_uint8 * 128)(*unique_id)
+            check(lib.ddm_comm_init(self.h, C.c_int(rank), C.c_int(world), uid))
+        check(lib.ddm_upload_operator(self.h, C.c_int64(S.n_own), C.c_int64(S.n_ghost), _p(S.rowptr, C.c_int64),
+                                      _p(S.col, C.c_int32), _p(S.val, C.c_double)))
+        self.n_own = S.n_own
+        if world > 1:
+            check(lib.ddm_upload_halo(self.h, C.c_int32(S.peers.size), _p(S.peers, C.c_int32), _p(S.send_ptr, C.c_int64),
+                                      _p(S.send_idx, C.c_int32), _p(S.recv_ptr, C.c_int64)))
+        a, b = S.sub_range
+        pou = np.concatenate([P.pou[i] for i in range(a, b)]).astype(np.float64) if b > a else np.zeros(0)
+        check(lib.ddm_upload_decomposition(self.h, C.c_int32(b - a), _p(S.sub_ptr, C.c_int64), _p(S.sub_dofs, C.c_int32),
+                                           _p(pou, C.c_double)))
+        for i in range(a, b):
+            F = P.factors[i]
+            check(lib.ddm_upload_factor(self.h, C.c_int32(i - a), C.c_int32(F.n), C.c_int32(F.nsuper),
+                                        _p(np.ascontiguousarray(F.super_, dtype=np.int32), C.c_int32),
+                                        _p(np.ascontiguousarray(F.pi, dtype=np.int64), C.c_int64),
+                                        _p(np.ascontiguousarray(F.px, dtype=np.int64), C.c_int64),
+                                        _p(np.ascontiguousarray(F.s, dtype=np.int32), C.c_int32),
+                                        _p(np.ascontiguousarray(F.x, dtype=np.float64), C.c_double),
+                                        _p(np.ascontiguousarray(F.perm, dtype=np.int32), C.c_int32)))
+        N0 = int(P.A0.shape[0])
+        self.N0 = N0 if with_coarse else 0
+        if with_coarse and N0 > 0:
+            k = np.array([P.Z[i].shape[1] for i in range(a, b)], dtype=np.int32)
+            Z = np.concatenate([P.Z[i].ravel(order="F") for i in range(a, b)]) if b > a else np.zeros(1)
+            A0 = np.ascontiguousarray(P.A0, dtype=np.float64)
+            check(lib.ddm_upload_coarse(self.h, _p(k, C.c_int32), _p(np.ascontiguousarray(Z), C.c_double), C.c_int32(N0),
+                                        C.c_int32(S.k_offset), _p(A0, C.c_double)))
+        check(lib.ddm_finalize(self.h))
+        return self
+
+    # -- helpers
+    def vector(self, values=None):
+        return DeviceVector(self, values)
+
+    def owned(self, global_vec):
+        """Restrict a unique-DOF vector to this rank's owned entries."""
+        return np.ascontiguousarray(np.asarray(global_vec)[self.shard.owned])
+
+    def stat(self, key):
+        v = C.c_double()
+        check(self.lib.ddm_get_stat(self.h, key.encode(), C.byref(v)))
+        return v.value
+
+    def timers(self, on=True):
+        check(self.lib.ddm_timers_enable(self.h, C.c_int(int(on))))
+        check(self.lib.ddm_timers_reset(self.h))
+
+    def timer(self, event):
+        ms, n = C.c_double(), C.c_int64()
+        check(self.lib.ddm_get_timer(self.h, event.encode(), C.byref(ms), C.byref(n)))
+        return ms.value, n.value
+
+    def launches(self):
+        return int(self.lib.ddm_kernel_launches(self.h))
+
+    def sync(self):
+        check(self.lib.ddm_sync(self.h))
+
+    def close(self):
+        if self.h:
+            self.lib.ddm_ctx_destroy(self.h)
+            self.h = C.c_void_p()
+
+
+class NonOverlappingOperator:
+    """y = A x and y += alpha A x (nonoverlapping_operator.hh:34-50)."""
+
+    category = "nonoverlapping"
+
+    def __init__(self, ctx):
+        self.ctx = ctx
+
+    def apply(self, x, y):
+        check(self.ctx.lib.ddm_op_apply(self.ctx.h, x.h, y.h))
+
+    def applyscaleadd(self, alpha, x, y):
+        check(self.ctx.lib.ddm_op_applyscaleadd(self.ctx.h, C.c_double(alpha), x.h, y.h))
+
+    def apply_host(self, x):
+        y = np.empty(self.ctx.n_own)
+        check(self.ctx.lib.ddm_op_apply_host(self.ctx.h, _p(np.ascontiguousarray(x, dtype=np.float64), C.c_double), _p(y, C.c_double)))
+        return y
+
+
+class NonOverlappingScalarProduct:
+    """Owner-masked dot and norm (nonoverlapping_operator.hh:76-83)."""
+
+    category = "nonoverlapping"
+
+    def __init__(self, ctx):
+        self.ctx = ctx
+
+    def dot(self, x, y):
+        out = C.c_double()
+        check(self.ctx.lib.ddm_dot(self.ctx.h, x.h, y.h, C.byref(out)))
+        return out.value
+
+    def norm(self, x):
+        out = C.c_double()
+        check(self.ctx.lib.ddm_norm(self.ctx.h, x.h, C.byref(out)))
+        return out.value
+
+
+class SchwarzPreconditioner:
+    """One-level overlapping Schwarz (schwarz.hh:115-149); type 'standard' or 'restricted' (:80-83)."""
+
+    category = "nonoverlapping"
+
+    def __init__(self, ctx, type="restricted"):
+        if type not in ("standard", "restricted"):
+            raise DDMError(f"Unknown Schwarz type '{type}'")  # schwarz.hh:83
+        self.ctx, self.type = ctx, STANDARD if type == "standard" else RESTRICTED
+
+    def pre(self, x, b):
+        pass
+
+    def post(self, x):
+        pass
+
+    def apply(self, x, d):
+        check(self.ctx.lib.ddm_schwarz_apply(self.ctx.h, C.c_int(self.type), d.h, x.h))
+
+
+class GalerkinPreconditioner:
+    """Coarse correction Z A0^{-1} Z^T (galerkin_preconditioner.hh:151-194)."""
+
+    category = "nonoverlapping"
+
+    def __init__(self, ctx):
+        self.ctx = ctx
+
+    def pre(self, x, b):
+        pass
+
+    def post(self, x):
+        pass
+
+    def apply(self, x, d):
+        check(self.ctx.lib.ddm_coarse_apply(self.ctx.h, d.h, x.h))
+
+
+class CombinedPreconditioner:
+    """Additive or multiplicative combination (combined_preconditioner.hh:127-163).
+
+    add() takes a SchwarzPreconditioner first and optionally a GalerkinPreconditioner, the order the
+    reference drivers use (examples/poisson.cc:305-306); both levels then run as one fused GPU pass.
+    """
+
+    category = "nonoverlapping"
+
+    def __init__(self, mode="additive"):
+        if mode not in ("additive", "multiplicative"):
+            raise DDMError(f"Unknown apply mode '{mode}'")  # combined_preconditioner.hh:66
+        self.mode = ADDITIVE if mode == "additive" else MULTIPLICATIVE
+        self.precs = []
+        self.op = None
+
+    def set_op(self, op):
+        self.op = op
+
+    def add(self, prec):
+        if getattr(prec, "category", None) != self.category:
+            raise DDMError("Preconditioner category mismatch")  # combined_preconditioner.hh:92-96
+        if not self.precs and not isinstance(prec, SchwarzPreconditioner):
+            raise DDMError("the first preconditioner must be the Schwarz level")
+        if self.precs and not isinstance(prec, GalerkinPreconditioner):
+            raise DDMError("the second preconditioner must be the Galerkin level")
+        self.precs.append(prec)
+
+    def pre(self, x, b):
+        pass
+
+    def post(self, x):
+        pass
+
+    def apply(self, x, d):
+        if not self.precs:
+            raise DDMError("No preconditioners added")
+        if self.mode == MULTIPLICATIVE and len(self.precs) > 1 and self.op is None:
+            raise DDMError("Multiplicative mode needs the operator, call set_op")  # combined_preconditioner.hh:147
+        s = self.precs[0]
+        check(s.ctx.lib.ddm_twolevel_apply(s.ctx.h, C.c_int(s.type), C.c_int(self.mode), C.c_int(int(len(self.precs) > 1)), d.h, x.h))
+
+    def apply_host(self, d):
+        s = self.precs[0]
+        x = np.empty(s.ctx.n_own)
+        check(s.ctx.lib.ddm_twolevel_apply_host(s.ctx.h, C.c_int(s.type), C.c_int(self.mode), C.c_int(int(len(self.precs) > 1)),
+                                                _p(np.ascontiguousarray(d, dtype=np.float64), C.c_double), _p(x, C.c_double)))
+        return x
+
+
+class InverseOperatorResult:
+    def __init__(self, iterations=0, converged=False, reduction=0.0, conv_rate=0.0, elapsed=0.0, history=None):
+        self.iterations, self.converged, self.reduction = iterations, converged, reduction
+        self.conv_rate, self.elapsed, self.history = conv_rate, elapsed, history
+
+
+class CGSolver:
+    """Dune::CGSolver (solvers.hh:279-340) over the three interfaces above.
+
+    apply() is the literal drop-in loop: every scalar comes back to the host exactly where
+    Dune::CGSolver reads it.  solve_device() runs the same recurrences with the scalars kept on the
+    GPU (ddm_pcg_solve).
+    """
+
+    def __init__(self, op, sp, prec, reduction=1e-8, maxit=100, verbose=0):
+        self.op, self.sp, self.prec = op, sp, prec
+        self.reduction, self.maxit, self.verbose = reduction, maxit, verbose
+
+    def apply(self, x, b):
+        hist = []
+        self.prec.pre(x, b)
+        self.op.applyscaleadd(-1.0, x, b)
+        d = self.sp.norm(b)
+        def0 = d
+        hist.append(d)
+        if not np.isfinite(d):
+            raise DDMError("CGSolver: defect is infinite or NaN")  # SolverAbort, solver.hh:458-466
+
+        def conv(v):
+            return v < def0 * self.reduction or v < 1e-30
+
+        i = 0
+        if not conv(d):
+            ctx = x.ctx
+            p, q = ctx.vector(), ctx.vector()
+            p.fill(0.0)
+            self.prec.apply(p, b)
+            rholast = self.sp.dot(p, b)
+            for i in range(1, self.maxit + 1):
+                self.op.apply(p, q)
+                alpha = self.sp.dot(p, q)
+                lam = 0.0 if d == 0.0 else rholast / alpha
+                x.axpy(lam, p)
+                b.axpy(-lam, q)
+                d = self.sp.norm(b)
+                hist.append(d)
+                if not np.isfinite(d):
+                    raise DDMError("CGSolver: defect is infinite or NaN")
+                if conv(d):
+                    break
+                q.fill(0.0)
+                self.prec.apply(q, b)
+                rho = self.sp.dot(q, b)
+                beta = 0.0 if d == 0.0 else rho / rholast
+                p *= beta
+                p += q
+                rholast = rho
+        self.prec.post(x)
+        red = d / def0 if def0 > 0 else 0.0
+        return InverseOperatorResult(i, conv(d), red, red ** (1.0 / i) if i else 0.0, 0.0, np.array(hist))
+
+    def solve_device(self, x, b):
+        s = self.prec.precs[0]
+        res = Result()
+        hist = np.zeros(self.maxit + 1)
+        check(s.ctx.lib.ddm_pcg_solve(s.ctx.h, b.h, x.h, C.c_double(self.reduction), C.c_int32(self.maxit), C.c_int(s.type),
+                                      C.c_int(self.prec.mode), C.c_int(int(len(self.prec.precs) > 1)), C.byref(res), _p(hist, C.c_double)))
+        return InverseOperatorResult(res.iterations, bool(res.converged), res.reduction, res.conv_rate, res.elapsed, hist[: res.iterations + 1])
+
+    def solve_host(self, b_host, x_host=None):
+        """End-to-end call with host buffers (H2D and D2H inside)."""
+        s = self.prec.precs[0]
+        b = np.array(b_host, dtype=np.float64)
+        x = np.zeros_like(b) if x_host is None else np.array(x_host, dtype=np.float64)
+        res = Result()
+        hist = np.zeros(self.maxit + 1)
+        check(s.ctx.lib.ddm_pcg_solve_host(s.ctx.h, _p(b, C.c_double), _p(x, C.c_double), C.c_double(self.reduction), C.c_int32(self.maxit),
+                                           C.c_int(s.type), C.c_int(self.prec.mode), C.c_int(int(len(self.prec.precs) > 1)), C.byref(res), _p(hist, C.c_double)))
+        return x, InverseOperatorResult(res.iterations, bool(res.converged), res.reduction, res.conv_rate, res.elapsed, hist[: res.iterations + 1])

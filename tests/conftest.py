@@ -1,0 +1,28 @@
+import os
+import sys
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.join(ROOT, "dune-ddm_b200"))
+sys.path.insert(0, ROOT)
+
+
+def pytest_configure(config):
+    config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box)")
+
+
+@pytest.fixture(scope="session")
+def small3d():
+    """3-D P1 Poisson, islands coefficient, 8 subdomains, overlap 2, GenEO (nev 6)."""
+    from ddm_b200.setup import problem
+
+    return problem.unitcube_p1(12, 8, overlap=2, nev=6, workers=1)
+
+
+@pytest.fixture(scope="session")
+def small2d():
+    """2-D P1 Poisson (config C1 shape at reduced size): 16 subdomains, overlap 2, GenEO (nev 8)."""
+    from ddm_b200.setup import problem
+
+    return problem.unitsquare_p1(40, 16, overlap=2, nev=8, workers=1)
