@@ -7,6 +7,7 @@
 #include <cooperative_groups.h>
 #include <cuda_runtime.h>
 #include <cusolverDn.h>
+#include <dlfcn.h>
 #include <nccl.h>
 
 #include <algorithm>
@@ -43,13 +44,55 @@ static int fail(const char *fmt, ...)
 #define NC(call)                                                                                         \
     do {                                                                                                 \
         ncclResult_t e_ = (call);                                                                        \
-        if (e_ != ncclSuccess) return fail("%s:%d %s: %s", __FILE__, __LINE__, #call, ncclGetErrorString(e_)); \
+        if (e_ != ncclSuccess) return fail("%s:%d %s: %s", __FILE__, __LINE__, #call, g_nccl.GetErrorString(e_)); \
     } while (0)
 #define CK(call)                                                                                         \
     do {                                                                                                 \
         int e_ = (call);                                                                                 \
         if (e_) return e_;                                                                               \
     } while (0)
+
+// NCCL is bound at run time (ddm_comm_init), preferring a libnccl the process has already loaded: a host
+// program that also uses torch.distributed must not end up with two NCCL versions in one address space.
+struct NcclApi {
+    void *h = nullptr;
+    ncclResult_t (*GetUniqueId)(ncclUniqueId *) = nullptr;
+    ncclResult_t (*CommInitRank)(ncclComm_t *, int, ncclUniqueId, int) = nullptr;
+    ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+    ncclResult_t (*GroupStart)() = nullptr;
+    ncclResult_t (*GroupEnd)() = nullptr;
+    ncclResult_t (*Send)(const void *, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*Recv)(void *, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*AllReduce)(const void *, void *, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t, cudaStream_t) = nullptr;
+    const char *(*GetErrorString)(ncclResult_t) = nullptr;
+};
+static NcclApi g_nccl;
+static int nccl_load()
+{
+    if (g_nccl.h) return 0;
+    void *h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_NOLOAD);
+    if (!h) {
+        const char *env = getenv("DDM_NCCL_LIB");
+        if (env) h = dlopen(env, RTLD_NOW | RTLD_GLOBAL);
+    }
+    if (!h) h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+    if (!h) return fail("cannot load libnccl.so.2: %s", dlerror());
+#define BIND(field, sym)                                                        \
+    *(void **)(&g_nccl.field) = dlsym(h, sym);                                  \
+    if (!g_nccl.field) return fail("libnccl.so.2 lacks %s", sym);
+    BIND(GetUniqueId, "ncclGetUniqueId")
+    BIND(CommInitRank, "ncclCommInitRank")
+    BIND(CommDestroy, "ncclCommDestroy")
+    BIND(GroupStart, "ncclGroupStart")
+    BIND(GroupEnd, "ncclGroupEnd")
+    BIND(Send, "ncclSend")
+    BIND(Recv, "ncclRecv")
+    BIND(AllReduce, "ncclAllReduce")
+    BIND(GetErrorString, "ncclGetErrorString")
+#undef BIND
+    g_nccl.h = h;
+    return 0;
+}
 
 extern "C" const char *ddm_last_error(void) { return g_err.c_str(); }
 extern "C" const char *ddm_version(void) { return "ddm_b200 0.1 (sm_100a)"; }
@@ -235,7 +278,7 @@ extern "C" int ddm_ctx_destroy(ddm_ctx *c)
         cudaEventDestroy(r.a);
         cudaEventDestroy(r.b);
     }
-    if (c->comm) ncclCommDestroy(c->comm);
+    if (c->comm) g_nccl.CommDestroy(c->comm);
     cudaStreamDestroy(c->s);
     delete c;
     return 0;
@@ -244,8 +287,9 @@ extern "C" int ddm_ctx_destroy(ddm_ctx *c)
 // ------------------------------------------------------------------------------------------------ comm
 extern "C" int ddm_comm_unique_id(uint8_t out[128])
 {
+    CK(nccl_load());
     ncclUniqueId id;
-    NC(ncclGetUniqueId(&id));
+    NC(g_nccl.GetUniqueId(&id));
     static_assert(sizeof(ncclUniqueId) == 128, "ncclUniqueId size");
     memcpy(out, &id, 128);
     return 0;
@@ -257,9 +301,10 @@ extern "C" int ddm_comm_init(ddm_ctx *c, int rank, int nranks, const uint8_t uid
     c->rank = rank;
     c->nranks = nranks;
     if (nranks > 1) {
+        CK(nccl_load());
         ncclUniqueId id;
         memcpy(&id, uid, 128);
-        NC(ncclCommInitRank(&c->comm, nranks, id, rank));
+        NC(g_nccl.CommInitRank(&c->comm, nranks, id, rank));
     }
     return 0;
 }
@@ -296,26 +341,26 @@ static int halo_forward(ddm_ctx *c, double *v)
     if (c->nranks == 1 || c->npeers == 0) return 0;
     const int64_t ns = c->send_ptr[c->npeers];
     if (ns) LAUNCH(c, pack_kernel, nblocks(ns), 256, ns, c->send_idx, v, c->sendbuf);
-    NC(ncclGroupStart());
+    NC(g_nccl.GroupStart());
     for (int p = 0; p < c->npeers; ++p) {
         const int64_t sc = c->send_ptr[p + 1] - c->send_ptr[p], rc = c->recv_ptr[p + 1] - c->recv_ptr[p];
-        if (sc) NC(ncclSend(c->sendbuf + c->send_ptr[p], sc, ncclDouble, c->peers[p], c->comm, c->s));
-        if (rc) NC(ncclRecv(v + c->n_own + c->recv_ptr[p], rc, ncclDouble, c->peers[p], c->comm, c->s));
+        if (sc) NC(g_nccl.Send(c->sendbuf + c->send_ptr[p], sc, ncclDouble, c->peers[p], c->comm, c->s));
+        if (rc) NC(g_nccl.Recv(v + c->n_own + c->recv_ptr[p], rc, ncclDouble, c->peers[p], c->comm, c->s));
     }
-    NC(ncclGroupEnd());
+    NC(g_nccl.GroupEnd());
     return 0;
 }
 // ghosts -> owners, summed in fixed peer order (addOwnerCopyToOwnerCopy / addOwnerCopyToAll, :362-387)
 static int halo_reverse_add(ddm_ctx *c, double *v)
 {
     if (c->nranks == 1 || c->npeers == 0) return 0;
-    NC(ncclGroupStart());
+    NC(g_nccl.GroupStart());
     for (int p = 0; p < c->npeers; ++p) {
         const int64_t sc = c->send_ptr[p + 1] - c->send_ptr[p], rc = c->recv_ptr[p + 1] - c->recv_ptr[p];
-        if (rc) NC(ncclSend(v + c->n_own + c->recv_ptr[p], rc, ncclDouble, c->peers[p], c->comm, c->s));
-        if (sc) NC(ncclRecv(c->recvbuf + c->send_ptr[p], sc, ncclDouble, c->peers[p], c->comm, c->s));
+        if (rc) NC(g_nccl.Send(v + c->n_own + c->recv_ptr[p], rc, ncclDouble, c->peers[p], c->comm, c->s));
+        if (sc) NC(g_nccl.Recv(c->recvbuf + c->send_ptr[p], sc, ncclDouble, c->peers[p], c->comm, c->s));
     }
-    NC(ncclGroupEnd());
+    NC(g_nccl.GroupEnd());
     for (int p = 0; p < c->npeers; ++p) { // one launch per peer: duplicates across peers add in peer order
         const int64_t sc = c->send_ptr[p + 1] - c->send_ptr[p];
         if (sc) LAUNCH(c, unpack_add_kernel, nblocks(sc), 256, sc, c->send_idx + c->send_ptr[p], c->recvbuf + c->send_ptr[p], v);
@@ -790,7 +835,7 @@ static int dot_dev(ddm_ctx *c, const double *x, const double *y, int slot)
 {
     LAUNCH(c, dot_partial_kernel, c->nred, 256, c->n_own, x, y, c->partial);
     LAUNCH(c, reduce_final_kernel, 1, 256, c->nred, c->partial, c->scal + slot);
-    if (c->nranks > 1) NC(ncclAllReduce(c->scal + slot, c->scal + slot, 1, ncclDouble, ncclSum, c->comm, c->s));
+    if (c->nranks > 1) NC(g_nccl.AllReduce(c->scal + slot, c->scal + slot, 1, ncclDouble, ncclSum, c->comm, c->s));
     return 0;
 }
 static int fetch_scalar(ddm_ctx *c, int slot, double *out)
@@ -834,7 +879,7 @@ static int coarse_solve(ddm_ctx *c)
     const int N0 = c->N0;
     if (c->nranks > 1) CU(cudaMemsetAsync(c->d0, 0, sizeof(double) * N0, c->s));
     LAUNCH(c, coarse_restrict_final_kernel, c->nsub, 64, c->nsub, c->seg_ptr, c->d_sub_k, c->d_koff, c->cpartial, c->kpad, c->d0);
-    if (c->nranks > 1) NC(ncclAllReduce(c->d0, c->d0, N0, ncclDouble, ncclSum, c->comm, c->s)); // gatherv (galerkin_preconditioner.hh:171)
+    if (c->nranks > 1) NC(g_nccl.AllReduce(c->d0, c->d0, N0, ncclDouble, ncclSum, c->comm, c->s)); // gatherv (galerkin_preconditioner.hh:171)
     const int grid = nblocks((int64_t)N0 * 32);
     // y = A0inv d0, then one refinement step: y += A0inv (d0 - A0 y)
     LAUNCH(c, dense_gemv_kernel, grid, 256, N0, c->A0inv, c->d0, c->y0, (const double *)nullptr, 1.0);
@@ -966,7 +1011,7 @@ extern "C" int ddm_pcg_solve(ddm_ctx *c, ddm_vec *b, ddm_vec *x, double reductio
             LAUNCH(c, cg_update_kernel, c->nred, 256, c->n_own, c->scal + cur, c->scal + 1, def == 0.0 ? 1 : 0, p->d, q->d, x->d,
                    b->d, c->partial);
             LAUNCH(c, reduce_final_kernel, 1, 256, c->nred, c->partial, c->scal + 2);
-            if (c->nranks > 1) NC(ncclAllReduce(c->scal + 2, c->scal + 2, 1, ncclDouble, ncclSum, c->comm, c->s));
+            if (c->nranks > 1) NC(g_nccl.AllReduce(c->scal + 2, c->scal + 2, 1, ncclDouble, ncclSum, c->comm, c->s));
             CK(fetch_scalar(c, 2, &def2));
             def = std::sqrt(def2);
             if (history) history[i] = def;

@@ -15,6 +15,7 @@
  * Vectors are indexed by unique global DOF; a reference rank's consistent local vector is the
  * restriction of that vector to the rank's index list.
  */
+#include "oracle.h"
 #include <math.h>
 #include <stdint.h>
 #include <stdlib.h>
@@ -85,31 +86,6 @@ void oracle_super_solve(int32_t n, int32_t nsuper, const int32_t *super, const i
     }
     for (int32_t k = 0; k < n; ++k) out[perm[k]] = y[k];
 }
-
-/* Setup products of all subdomains, flat (see oracle/oracle.py for how they are packed). */
-typedef struct {
-    int32_t nsub;
-    int64_t n;              /* unique global DOFs */
-    const int64_t *sub_ptr; /* nsub+1 */
-    const int32_t *sub_dofs;/* R_i index lists */
-    const double *pou;      /* D_i, same layout as sub_dofs */
-    /* factors, one entry per subdomain */
-    const int32_t *nsuper;
-    const int32_t **super;
-    const int64_t **pi, **px;
-    const int32_t **s;
-    const double **x;
-    const int32_t **perm;
-    /* coarse space */
-    const int64_t *z_ptr;   /* nsub+1 offsets into Z (column-major n_i x k_i blocks) */
-    const int32_t *k_off;   /* nsub+1 exclusive scan of k_i */
-    const double *Z;
-    const double *A0chol;   /* dense lower Cholesky factor of A0, row-major N0 x N0 */
-    /* operator (for the multiplicative combine) */
-    const int64_t *rowptr;
-    const int32_t *col;
-    const double *val;
-} oracle_setup;
 
 /* SchwarzPreconditioner::apply, /root/reference/dune/ddm/schwarz.hh:115-149.
  * restricted != 0: x = sum_i R_i^T D_i A_i^{-1} R_i d ; else x = sum_i R_i^T A_i^{-1} R_i d.
