@@ -111,14 +111,27 @@ def _sub_job(i):
 def build(coords, cells, Ke, dirichlet, rhs, cell_part, nsub, overlap=2, pou_kind="distance", shrink=0,
           coarse="geneo", nev=16, shift=1e-3, eig_tol=1e-5, leaf_size=32, workers=None, meta=None):
     """Generic pipeline from an element-wise description to SetupProducts."""
+    import time
+
+    verbose = bool(os.environ.get("DDM_SETUP_VERBOSE"))
+    t0 = [time.time()]
+
+    def tick(what):
+        if verbose:
+            print(f"[setup] {what}: {time.time() - t0[0]:.2f}s", flush=True)
+        t0[0] = time.time()
+
     n = coords.shape[0]
     A_full = fem.assemble(n, cells, Ke)
     A = fem.eliminate_dirichlet(A_full, dirichlet)
     b = np.where(dirichlet, 0.0, rhs)
+    tick("assemble")
     novlp, owner = decomp.nonoverlapping_sets(n, cells, cell_part, nsub)
     subs = decomp.grow_overlap(A_full, novlp, overlap)
+    tick("overlap")
     bmasks = decomp.boundary_masks(A_full, subs)
     pou = decomp.partition_of_unity(A_full, subs, bmasks, owner, pou_kind, shrink, overlap)
+    tick("pou")
     shared = np.zeros(n, dtype=np.int32)
     for s in subs:
         shared[s] += 1
@@ -136,7 +149,9 @@ def build(coords, cells, Ke, dirichlet, rhs, cell_part, nsub, overlap=2, pou_kin
         for i in range(nsub):
             _, factors[i], Z[i] = _sub_job(i)
     _G.clear()
+    tick("factor + coarse basis")
     A0, off, _ = coarse_mod.galerkin_matrix(A, subs, Z)
+    tick("galerkin")
     m = dict(meta or {})
     m.update(nsub=nsub, overlap=overlap, pou=pou_kind, coarse=coarse, nev=nev, n=int(n), N0=int(A0.shape[0]))
     return SetupProducts(A=A, b=b, owner=owner, subs=subs, pou=pou, factors=factors, Z=Z, A0=A0, coords=coords,
