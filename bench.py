@@ -1,0 +1,320 @@
+#!/usr/bin/env python
+"""Benchmark of the solve phase: two-level additive Schwarz PCG to 1e-8 (BASELINE.json metric).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference] [--ncell C] [--nsub S] [--coarse geneo|pou]
+
+A step = one complete solve phase of the workload: PCG (Dune::CGSolver recurrences) preconditioned with the two-level
+additive Schwarz method, from x0 = 0 to a defect reduction of 1e-8.  The workload is BASELINE.json configs[1]
+("3D Poisson, heterogeneous coefficient, 64 subdomains, 2-level GenEO PCG") on a Kuhn-triangulated unit cube
+(the reference's data/unitcube.msh does not exist on the GPU box); with N GPUs the box grows to 64 subdomains per GPU
+(weak scaling).  Setup (mesh, assembly, factorisation, GenEO) runs on the host and is not timed, as in the reference's
+own "Total/Linear solve" event (examples/poisson.cc:171-174).
+Prints ONE JSON line on rank 0.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.join(ROOT, "dune-ddm_b200"))
+sys.path.insert(0, ROOT)
+
+import numpy as np  # noqa: E402
+
+METRIC = "schwarz_pcg_solved_dofs_per_second_to_1e-8"
+UNIT = "MDOF/s"
+REDUCTION = 1e-8
+MAXIT = 500
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--ncell", type=int, default=int(os.environ.get("DDM_BENCH_NCELL", 112)), help="cells per unit length")
+    ap.add_argument("--nsub", type=int, default=64, help="subdomains per GPU")
+    ap.add_argument("--coarse", default="geneo", choices=["geneo", "pou"])
+    ap.add_argument("--nev", type=int, default=16)
+    ap.add_argument("--overlap", type=int, default=2)
+    ap.add_argument("--cpu-seconds", type=float, default=20.0, help="budget of the cpu_baseline sample")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+def gpu_grid(n):
+    return {1: (1, 1, 1), 2: (2, 1, 1), 4: (2, 2, 1), 8: (2, 2, 2)}.get(n) or (n, 1, 1)
+
+
+def workload_name(a, world):
+    g = gpu_grid(world)
+    shape = tuple(a.ncell * k for k in g)
+    return (f"3D P1 Poisson, islands coefficient (poisson_coefficient.lua), Kuhn mesh {shape[0]}x{shape[1]}x{shape[2]} cells, "
+            f"{a.nsub * world} subdomains (RCB), overlap {a.overlap}, {a.coarse} coarse space nev {a.nev}, additive, CG 1e-8")
+
+
+def build_problem(a, world):
+    from ddm_b200.setup import fem, mesh, problem
+
+    g = gpu_grid(world)
+    shape = tuple(a.ncell * k for k in g)
+    coords, cells = mesh.structured_simplices(shape, lengths=tuple(float(k) for k in g))
+
+    def kappa(cent):  # the unit-cube pattern tiled over the box
+        return fem.kappa_islands(cent - np.floor(cent))
+
+    return problem.poisson_simplex(coords, cells, a.nsub * world, kappa_fn=kappa, xmax=float(g[0]), overlap=a.overlap,
+                                   coarse=a.coarse, nev=a.nev, meta=dict(mesh=f"kuhn-{shape}"))
+
+
+class ClockSampler:
+    """nvidia-smi clocks and throttle reasons during the timed region (B200_PROFILING.md)."""
+
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index=0):
+        self.rows, self.proc, self.index = [], None, index
+
+    def __enter__(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=lambda: self.rows.extend(self.proc.stdout), daemon=True)
+            self.t.start()
+        except OSError:
+            self.proc = None
+        return self
+
+    def __exit__(self, *exc):
+        if self.proc:
+            time.sleep(0.12)
+            self.proc.terminate()
+            self.t.join(timeout=2)
+
+    def summary(self):
+        sm, mx, reasons = [], 0.0, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            f = [x.strip() for x in r.split(",")]
+            if len(f) < 6:
+                continue
+            try:
+                sm.append(float(f[0]))
+                mx = max(mx, float(f[1]))
+            except ValueError:
+                continue
+            for nm, v in zip(names, f[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": mx or None, "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def dist_env():
+    rank, world, local = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1)), int(os.environ.get("LOCAL_RANK", 0))
+    return rank, world, local
+
+
+def cpu_baseline_sample(P, its_full, budget_s, nthreads):
+    """The oracle (CPU restatement, all host threads) on a bounded sample: the first m PCG iterations of the same
+    solve, extrapolated to the full iteration count.  oracle/ is used here only as the timed baseline."""
+    from oracle import oracle
+
+    O = oracle.Oracle(P, nthreads=nthreads)
+    t0 = time.perf_counter()
+    O.pcg(P.b, reduction=REDUCTION, maxit=1)
+    t1 = time.perf_counter() - t0  # 2 applies + 2 SpMV
+    m = int(max(1, min(its_full, (budget_s - t1) / max(t1 / 2, 1e-9))))
+    t0 = time.perf_counter()
+    _, it, conv, _ = O.pcg(P.b, reduction=REDUCTION, maxit=m)
+    t = time.perf_counter() - t0
+    t_full = t * (its_full + 1) / (it + 1)  # it iterations cost it+1 applies
+    return {"value": P.n / t_full / 1e6, "unit": UNIT, "cores": nthreads, "kind": "port",
+            "sample": f"first {it} of {its_full} PCG iterations of the same solve ({t:.1f} s measured, extrapolated by apply count)",
+            "seconds_full_solve_est": t_full}
+
+
+def run_reference(a):
+    """Reference arm: the reference's CPU algorithm for the path (oracle port; the reference binary itself needs
+    MPI + SuiteSparse + Eigen, absent from this image) on all host threads, same config, metric and unit."""
+    rank, world, _ = dist_env()
+    if rank != 0:
+        return
+    from oracle import oracle
+
+    P = build_problem(a, max(world, a.gpus))
+    nthreads = oracle.lib().oracle_max_threads()
+    O = oracle.Oracle(P, nthreads=nthreads)
+    t0 = time.perf_counter()
+    _, its_full, conv, hist = O.pcg(P.b, reduction=REDUCTION, maxit=MAXIT)  # full solve once: iteration count + warm-up
+    t_full_once = time.perf_counter() - t0
+    m = int(max(1, min(its_full, 30.0 / max(t_full_once / (its_full + 1), 1e-9))))
+    for _ in range(max(0, a.warmup - 1)):
+        O.pcg(P.b, reduction=REDUCTION, maxit=min(m, 2))
+    ts = []
+    for _ in range(a.steps):
+        t0 = time.perf_counter()
+        _, it, _, _ = O.pcg(P.b, reduction=REDUCTION, maxit=m)
+        ts.append((time.perf_counter() - t0) * (its_full + 1) / (it + 1))
+    t = float(np.mean(ts))
+    val = P.n / t / 1e6
+    line = {"impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": a.gpus, "steps": a.steps, "warmup": a.warmup,
+            "ms_per_step": t * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": workload_name(a, max(world, a.gpus)), "dofs": int(P.n), "iterations": int(its_full), "converged": bool(conv)},
+            "cpu_baseline": {"value": val, "unit": UNIT, "cores": nthreads, "kind": "port",
+                             "sample": f"each step = first {m} of {its_full} PCG iterations, extrapolated by apply count; full solve measured once: {t_full_once:.1f} s"},
+            "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+
+
+def run_b200(a):
+    rank, world, local = dist_env()
+    import torch
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the solve phase has no CPU path (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local)
+    import torch.distributed as dist
+
+    uid = None
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    from ddm_b200 import api, lib
+
+    t0 = time.perf_counter()
+    P = build_problem(a, world)
+    if rank == 0:
+        print(f"[bench] host setup {time.perf_counter() - t0:.1f} s: n={P.n} nsub={P.nsub} N0={P.A0.shape[0]} "
+              f"nnz(L)={sum(F.nnz_lower() for F in P.factors) / 1e6:.1f} M", file=sys.stderr, flush=True)
+    t0 = time.perf_counter()
+    if world > 1:
+        import ctypes as C
+
+        buf = (C.c_uint8 * 128)()
+        if rank == 0:
+            api.check(lib.load().ddm_comm_unique_id(buf))
+        t = torch.tensor(list(buf), dtype=torch.uint8, device="cuda")
+        dist.broadcast(t, 0)
+        uid = t.cpu().tolist()
+    ctx = api.Context.from_products(P, device=local, rank=rank, world=world, unique_id=uid)
+    if rank == 0:
+        print(f"[bench] upload + device schedules {time.perf_counter() - t0:.1f} s", file=sys.stderr, flush=True)
+    op, sp = api.NonOverlappingOperator(ctx), api.NonOverlappingScalarProduct(ctx)
+    Cp = api.CombinedPreconditioner("additive")
+    Cp.set_op(op)
+    Cp.add(api.SchwarzPreconditioner(ctx, "standard"))
+    Cp.add(api.GalerkinPreconditioner(ctx))
+    cg = api.CGSolver(op, sp, Cp, reduction=REDUCTION, maxit=MAXIT)
+    b_own = ctx.owned(P.b)
+    x, b = ctx.vector(), ctx.vector()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        ctx.sync()
+        torch.cuda.synchronize()
+
+    def step():
+        x.fill(0.0)
+        b.upload(b_own)  # b is overwritten by the defect (solvers.hh:284): restore it, device resident from here on
+        return cg.solve_device(x, b)
+
+    for _ in range(a.warmup):
+        res = step()
+    # ---- timed region: K solves, inputs resident in HBM, CUDA events on the library's stream
+    ctx.timers(True)
+    l0 = ctx.launches()
+    barrier()
+    with ClockSampler(local) as clk:
+        t_wall = time.perf_counter()
+        dev_ms = 0.0
+        for _ in range(a.steps):
+            x.fill(0.0)
+            b.upload(b_own)
+            ctx.stopwatch_start()
+            res = cg.solve_device(x, b)
+            dev_ms += ctx.stopwatch_stop()
+        barrier()
+        t_wall = time.perf_counter() - t_wall
+    launches = ctx.launches() - l0
+    timers = {ev: ctx.timer(ev) for ev in ("Schwarz/local solve fwd", "Schwarz/local solve bwd", "Schwarz/local solve", "Schwarz/get defect",
+                                          "Schwarz/add solution", "GalerkinPrec/coarse solve", "CombinedPreconditioner/apply", "Operator/apply")}
+    ctx.timers(False)
+    # ---- e2e: the same solve through the host-buffer entry (H2D of b and x0, D2H of x and the defect, every step)
+    for _ in range(min(2, a.warmup)):
+        cg.solve_host(b_own)
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(a.steps):
+        xh, rh = cg.solve_host(b_own)
+    barrier()
+    t_e2e = time.perf_counter() - t0
+    # ---- reduce over ranks
+    vals = torch.tensor([dev_ms, t_wall, t_e2e], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(vals, op=dist.ReduceOp.MAX)
+    dev_ms, t_wall, t_e2e = vals.tolist()
+    stats = {k: ctx.stat(k) for k in ("trisolve_fwd", "trisolve_bwd", "trisolve_stored", "spmv", "restrict", "prolong", "coarse", "factor_nnz")}
+    if rank != 0:
+        if world > 1:
+            dist.barrier()
+        return
+    n = P.n
+    ms_step = dev_ms / a.steps
+    value = n / (ms_step * 1e-3) / 1e6
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except OSError:
+        pass
+    peak, peak_src = (peaks["hbm_gbs"], "measured (MEASURED_PEAKS.json hbm_gbs)") if "hbm_gbs" in peaks else (6650.0, "fallback (B200_PROFILING.md)")
+    # dominant kernel: the forward triangular sweep (the backward sweep is reported beside it)
+    kern = {}
+    for name, ev in (("trisolve_fwd", "Schwarz/local solve fwd"), ("trisolve_bwd", "Schwarz/local solve bwd")):
+        ms, calls = timers[ev]
+        kern[name] = {"ms": ms / max(calls, 1), "GBps": stats[name] / (ms / max(calls, 1) * 1e-3) / 1e9 if ms > 0 else None, "launches": calls}
+    dom = max(kern, key=lambda k: kern[k]["ms"])
+    apply_ms, apply_calls = timers["CombinedPreconditioner/apply"]
+    apply_bytes = stats["trisolve_fwd"] + stats["trisolve_bwd"] + stats["restrict"] + stats["prolong"] + stats["coarse"]
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": a.warmup, "ms_per_step": ms_step,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": workload_name(a, world), "dofs": int(n), "subdomains": int(P.nsub), "coarse_dim": int(P.A0.shape[0]),
+                   "factor_nnz": stats["factor_nnz"], "iterations": int(res.iterations), "converged": bool(res.converged),
+                   "l2_policy": "inputs larger than L2 (factors %.1f GB per sweep vs 126 MB L2)" % (stats["trisolve_stored"] / 1e9)},
+        "time_to_1e-8_s": ms_step * 1e-3, "wall_ms_per_step": t_wall / a.steps * 1e3,
+        "precond_apply": {"ms": apply_ms / max(apply_calls, 1), "algorithmic_GB": apply_bytes / 1e9,
+                          "GBps": apply_bytes / (apply_ms / max(apply_calls, 1) * 1e-3) / 1e9 if apply_ms > 0 else None,
+                          "frac_of_peak": apply_bytes / (apply_ms / max(apply_calls, 1) * 1e-3) / 1e9 / peak if apply_ms > 0 else None},
+        "e2e": {"value": n / (t_e2e / a.steps) / 1e6, "unit": UNIT, "h2d_bytes_per_step": int(2 * 8 * ctx.n_own), "d2h_bytes_per_step": int(2 * 8 * ctx.n_own)},
+        "gpu_launches": int(launches),
+        "roofline": {"bound": "hbm", "kernel": f"{dom}_kernel", "achieved": kern[dom]["GBps"], "peak": peak, "unit": "GB/s",
+                     "frac": kern[dom]["GBps"] / peak if kern[dom]["GBps"] else None, "traffic": None, "peak_source": peak_src,
+                     "algorithmic_bytes_per_launch": stats[dom], "ms_per_launch": kern[dom]["ms"], "kernels": kern},
+        "timers_ms_per_call": {k: (v[0] / max(v[1], 1)) for k, v in timers.items()},
+        "clocks": clk.summary(),
+    }
+    if not a.no_cpu_baseline:
+        from oracle import oracle
+
+        line["cpu_baseline"] = cpu_baseline_sample(P, int(res.iterations), a.cpu_seconds, oracle.lib().oracle_max_threads()) if world == 1 else None
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+
+
+def main():
+    a = parse()
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_b200(a)
+
+
+if __name__ == "__main__":
+    main()

@@ -176,6 +176,7 @@ struct ddm_ctx {
     // stats / timers
     std::map<std::string, double> stats;
     bool timers_on = false;
+    cudaEvent_t sw0 = nullptr, sw1 = nullptr;
     std::vector<TimerRec> trecs;
     std::map<std::string, std::pair<double, int64_t>> tacc;
 };
@@ -894,11 +895,13 @@ static int trisolve(ddm_ctx *c)
     CU(cudaMemsetAsync(c->cnt, 0, sizeof(int) * (2 * (size_t)c->nchunks + 2), c->s));
     int *cnt_f = c->cnt, *cnt_b = c->cnt + c->nchunks, *tick_f = c->cnt + 2 * c->nchunks, *tick_b = tick_f + 1;
     {
+        ScopedTimer tf(c, "Schwarz/local solve fwd");
         void *args[] = {&c->fwd_tasks, &c->n_fwd, &c->W, &c->X, &c->need, &cnt_f, &tick_f};
         CU(cudaLaunchCooperativeKernel((void *)trisolve_fwd_kernel, dim3(c->tri_grid), dim3(256), args, 0, c->s));
         c->launches++;
     }
     if (c->n_bwd > 0) {
+        ScopedTimer tb(c, "Schwarz/local solve bwd");
         void *args[] = {&c->bwd_tasks, &c->n_bwd, &c->X, &c->nslices, &cnt_b, &tick_b};
         CU(cudaLaunchCooperativeKernel((void *)trisolve_bwd_kernel, dim3(c->tri_grid), dim3(256), args, 0, c->s));
         c->launches++;
@@ -1144,6 +1147,25 @@ extern "C" int ddm_get_timer(ddm_ctx *c, const char *event, double *total_ms, in
     }
     *total_ms = it->second.first;
     *calls = it->second.second;
+    return 0;
+}
+extern "C" int ddm_stopwatch_start(ddm_ctx *c)
+{
+    if (!c->sw0) {
+        CU(cudaEventCreate(&c->sw0));
+        CU(cudaEventCreate(&c->sw1));
+    }
+    CU(cudaEventRecord(c->sw0, c->s));
+    return 0;
+}
+extern "C" int ddm_stopwatch_stop(ddm_ctx *c, double *ms)
+{
+    if (!c->sw0) return fail("stopwatch was not started");
+    CU(cudaEventRecord(c->sw1, c->s));
+    CU(cudaEventSynchronize(c->sw1));
+    float f = 0;
+    CU(cudaEventElapsedTime(&f, c->sw0, c->sw1));
+    *ms = f;
     return 0;
 }
 extern "C" int64_t ddm_kernel_launches(ddm_ctx *c) { return c->launches; }

@@ -149,6 +149,14 @@ class Context:
         check(self.lib.ddm_get_timer(self.h, event.encode(), C.byref(ms), C.byref(n)))
         return ms.value, n.value
 
+    def stopwatch_start(self):
+        check(self.lib.ddm_stopwatch_start(self.h))
+
+    def stopwatch_stop(self):
+        ms = C.c_double()
+        check(self.lib.ddm_stopwatch_stop(self.h, C.byref(ms)))
+        return ms.value
+
     def launches(self):
         return int(self.lib.ddm_kernel_launches(self.h))
 

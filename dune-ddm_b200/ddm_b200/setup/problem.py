@@ -160,15 +160,15 @@ def build(coords, cells, Ke, dirichlet, rhs, cell_part, nsub, overlap=2, pou_kin
 
 
 # ----------------------------------------------------------------------------- named configurations
-def poisson_simplex(coords, cells, nsub, kappa_fn=fem.kappa_islands, **kw):
-    """P1 Poisson with Dirichlet data g = 1 - x on x in {0, 1} (poisson_coefficient.lua:1-3,38-44)."""
+def poisson_simplex(coords, cells, nsub, kappa_fn=fem.kappa_islands, xmax=1.0, **kw):
+    """P1 Poisson with Dirichlet data g = 1 - x/xmax on x in {0, xmax} (poisson_coefficient.lua:1-3,38-44)."""
     d = coords.shape[1]
     cent = coords[cells].mean(axis=1)
     Ke = fem.p1_element_matrices(coords, cells, kappa_fn(cent))
-    dirichlet = (coords[:, 0] < 1e-6) | (coords[:, 0] > 1.0 - 1e-6)
+    dirichlet = (coords[:, 0] < 1e-6) | (coords[:, 0] > xmax - 1e-6)
     n = coords.shape[0]
     # residual at the Dirichlet lift x0 (g on the boundary, 0 inside): d = A_full x0 - f, f = 0
-    x0 = np.where(dirichlet, 1.0 - coords[:, 0], 0.0)
+    x0 = np.where(dirichlet, 1.0 - coords[:, 0] / xmax, 0.0)
     rhs = fem.assemble(n, cells, Ke) @ x0
     part = decomp.rcb_partition(cent, nsub)
     meta = dict(kw.pop("meta", {}), problem="poisson-p1", dim=d)

@@ -158,6 +158,9 @@ int ddm_get_stat(ddm_ctx *ctx, const char *key, double *value);
 int ddm_timers_enable(ddm_ctx *ctx, int on);
 int ddm_timers_reset(ddm_ctx *ctx);
 int ddm_get_timer(ddm_ctx *ctx, const char *event, double *total_ms, int64_t *calls);
+/* CUDA-event stopwatch on the context's stream (the stream every kernel of this library is launched on). */
+int ddm_stopwatch_start(ddm_ctx *ctx);
+int ddm_stopwatch_stop(ddm_ctx *ctx, double *elapsed_ms);
 int64_t ddm_kernel_launches(ddm_ctx *ctx);
 int ddm_sync(ddm_ctx *ctx);
 
