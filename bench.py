@@ -44,6 +44,8 @@ def parse():
     ap.add_argument("--overlap", type=int, default=2)
     ap.add_argument("--cpu-seconds", type=float, default=20.0, help="budget of the cpu_baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--pack", default=None, help=".ddmpack cache of the setup products: loaded if present, else built and saved")
+    ap.add_argument("--setup-only", action="store_true", help="build (and save) the setup products, then exit")
     return ap.parse_args()
 
 
@@ -59,8 +61,17 @@ def workload_name(a, world):
 
 
 def build_problem(a, world):
-    from ddm_b200.setup import fem, mesh, problem
+    from ddm_b200.setup import fem, mesh, pack, problem
 
+    if a.pack and os.path.exists(a.pack):
+        return pack.load_products(a.pack)
+    P = _build_problem(a, world, fem, mesh, problem)
+    if a.pack:
+        pack.save_products(a.pack, P)
+    return P
+
+
+def _build_problem(a, world, fem, mesh, problem):
     g = gpu_grid(world)
     shape = tuple(a.ncell * k for k in g)
     coords, cells = mesh.structured_simplices(shape, lengths=tuple(float(k) for k in g))
@@ -310,6 +321,9 @@ def run_b200(a):
 
 def main():
     a = parse()
+    if a.setup_only:
+        build_problem(a, max(a.gpus, dist_env()[1]))
+        return
     if a.impl == "reference":
         run_reference(a)
     else:

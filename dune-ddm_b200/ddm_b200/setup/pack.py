@@ -83,3 +83,27 @@ def products_to_arrays(P) -> dict:
 
 def save_products(path, P):
     write(path, products_to_arrays(P))
+
+
+def load_products(path):
+    """Inverse of save_products (coords / dirichlet / meta are not stored: they are setup-only)."""
+    import scipy.sparse as sp
+
+    from . import factor
+    from .problem import SetupProducts
+
+    d = read(path)
+    n, ns = int(d["n"][0]), int(d["nsub"][0])
+    A = sp.csr_matrix((d["A_val"], d["A_col"], d["A_rowptr"]), shape=(n, n))
+    sub_ptr, k = d["sub_ptr"], d["k"]
+    subs = [d["sub_dofs"][sub_ptr[i] : sub_ptr[i + 1]].astype(np.int64) for i in range(ns)]
+    pou = [d["pou"][sub_ptr[i] : sub_ptr[i + 1]] for i in range(ns)]
+    Z, zo = [], 0
+    for i in range(ns):
+        ni = int(sub_ptr[i + 1] - sub_ptr[i])
+        Z.append(np.asfortranarray(d["Z"][zo : zo + ni * int(k[i])].reshape((ni, int(k[i])), order="F")))
+        zo += ni * int(k[i])
+    factors = [factor.SupernodalFactor(n=subs[i].size, perm=d[f"F{i}_perm"], super_=d[f"F{i}_super"], pi=d[f"F{i}_pi"],
+                                       px=d[f"F{i}_px"], s=d[f"F{i}_s"], x=d[f"F{i}_x"]) for i in range(ns)]
+    return SetupProducts(A=A, b=d["b"], owner=d["owner"], subs=subs, pou=pou, factors=factors, Z=Z, A0=d["A0"],
+                         n_novlp=d["n_novlp"], meta=dict(n=n, nsub=ns, N0=int(d["A0"].shape[0])))
