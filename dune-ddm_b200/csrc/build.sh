@@ -6,5 +6,5 @@ OUT="$HERE/../libddm_b200.so"
 NVCC=${NVCC:-/usr/local/cuda/bin/nvcc}
 $NVCC -std=c++17 -O3 -lineinfo -gencode arch=compute_100a,code=sm_100a \
   -Xcompiler -fPIC -shared ${DDM_PTXAS_V:+-Xptxas -v} \
-  -o "$OUT" "$HERE/ddm_b200.cu" -lcusolver -ldl
+  -o "$OUT" "$HERE/ddm_b200.cu" -lcusolver -lcublas -ldl
 echo "built $OUT"

@@ -2,10 +2,11 @@
 // Host side of the library: context, uploads, factor re-layout, task schedules, orchestration of the
 // apply path and the device-resident PCG loop.  No CPU compute path exists behind these entry points.
 #include "../../include/ddm_b200.h"
-#include "kernels.cuh"
+#include "trisolve.cuh"
 
 #include <cooperative_groups.h>
 #include <cuda_runtime.h>
+#include <cublas_v2.h>
 #include <cusolverDn.h>
 #include <dlfcn.h>
 #include <nccl.h>
@@ -101,15 +102,13 @@ extern "C" const char *ddm_version(void) { return "ddm_b200 0.1 (sm_100a)"; }
 struct SubFactor {
     int32_t n = 0;
     std::vector<int32_t> perm;
-    // chunks (block columns of width <= 32), in elimination order
-    std::vector<int32_t> col0, w, parent, level, ntiles;
-    std::vector<int64_t> tile_off;   // offset (doubles) of the chunk's first tile in `panel`
-    std::vector<int64_t> row_off;    // offset of the chunk's row list in `rowidx`
-    std::vector<int64_t> dinv_off;   // offset of the chunk's inverse diagonal block in `dinv`
-    double *panel = nullptr;         // device
-    int32_t *rowidx = nullptr;       // device (absolute W offsets, filled at finalize)
-    double *dinv = nullptr;          // device
-    std::vector<int32_t> rows_host;  // pivot-numbered rows, -1 padding (becomes rowidx)
+    // supernodes in elimination order
+    std::vector<int32_t> col0, cw, nb, parent, level;
+    std::vector<int64_t> tile_off;  // offset (doubles) of the supernode's first tile in `panel`
+    std::vector<int64_t> row_off;   // offset of the supernode's row targets in `rowidx`
+    double *panel = nullptr;        // device: tiles of [D^{-1}; -Lt] per supernode (trisolve.cuh)
+    int32_t *rowidx = nullptr;      // device: absolute WX offsets, filled at finalize
+    std::vector<int32_t> rows_host; // -1 padding, -2-k = X position k (diagonal rows), >= 0 W position (below rows)
     int64_t panel_doubles = 0, nnz_lower = 0;
     bool present = false;
 };
@@ -153,11 +152,10 @@ struct ddm_ctx {
     double *cpartial = nullptr;
     int32_t *dptr = nullptr, *dpos = nullptr;
     TriTask *fwd_tasks = nullptr, *bwd_tasks = nullptr;
-    int32_t n_fwd = 0, n_bwd = 0, nchunks = 0;
-    int32_t *need = nullptr, *nslices = nullptr;
-    int *cnt = nullptr; // [2*nchunks + 2]: fwd counters, bwd counters, tickets
+    int32_t n_fwd = 0, n_bwd = 0, nsn = 0;
+    int *cnt = nullptr; // [2*nsn + 2]: fwd counters, bwd counters, tickets
     int tri_grid = 0;
-    int tpt = 4;
+    cublasHandle_t blas = nullptr;
     // reductions / scalars
     int nred = 0;
     double *partial = nullptr, *scal = nullptr; // scal[8] device scalars
@@ -245,7 +243,6 @@ extern "C" int ddm_ctx_create(int device, ddm_ctx **out)
     CU(cudaMalloc((void **)&c->scal, sizeof(double) * 16));
     CU(cudaMemset(c->scal, 0, sizeof(double) * 16));
     CU(cudaMallocHost((void **)&c->h_scal, sizeof(double) * 16));
-    if (const char *e2 = getenv("DDM_TPT")) c->tpt = std::max(1, atoi(e2));
     *out = c;
     return 0;
 }
@@ -254,7 +251,6 @@ static void free_factor(SubFactor &f)
 {
     cudaFree(f.panel);
     cudaFree(f.rowidx);
-    cudaFree(f.dinv);
     f = SubFactor();
 }
 
@@ -268,9 +264,9 @@ extern "C" int ddm_ctx_destroy(ddm_ctx *c)
     for (auto &v : c->hv) ddm_vec_destroy(v);
     for (auto &v : c->tmp) ddm_vec_destroy(v);
     for (auto &f : c->fac) free_factor(f);
-    void *ptrs[] = {c->rowptr, c->col, c->val, c->A0, c->A0inv, c->d0, c->y0, c->r0, c->gidx, c->pouP, c->Zp, c->W, c->X,
+    void *ptrs[] = {c->rowptr, c->col, c->val, c->A0, c->A0inv, c->d0, c->y0, c->r0, c->gidx, c->pouP, c->Zp, c->W,
                     c->zoff, c->d_sub_n, c->d_sub_k, c->d_koff, c->seg_ptr, c->segs, c->cpartial, c->dptr, c->dpos,
-                    c->fwd_tasks, c->bwd_tasks, c->need, c->nslices, c->cnt, c->partial, c->scal, c->send_idx, c->sendbuf,
+                    c->fwd_tasks, c->bwd_tasks, c->cnt, c->partial, c->scal, c->send_idx, c->sendbuf,
                     c->recvbuf};
     for (void *p : ptrs) cudaFree(p);
     cudaFreeHost(c->h_scal);
@@ -280,6 +276,11 @@ extern "C" int ddm_ctx_destroy(ddm_ctx *c)
         cudaEventDestroy(r.b);
     }
     if (c->comm) g_nccl.CommDestroy(c->comm);
+    if (c->blas) cublasDestroy(c->blas);
+    if (c->sw0) {
+        cudaEventDestroy(c->sw0);
+        cudaEventDestroy(c->sw1);
+    }
     cudaStreamDestroy(c->s);
     delete c;
     return 0;
@@ -325,6 +326,11 @@ extern "C" int ddm_upload_halo(ddm_ctx *c, int32_t npeers, const int32_t *peers,
     return 0;
 }
 
+__global__ void set_identity_kernel(int n, double *M)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) M[(int64_t)i * n + i] = 1.0;
+}
 __global__ void pack_kernel(int64_t n, const int32_t *__restrict__ idx, const double *__restrict__ v, double *__restrict__ buf)
 {
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -424,98 +430,166 @@ extern "C" int ddm_upload_factor(ddm_ctx *c, int32_t sub, int32_t n, int32_t nsu
     if (F.present) free_factor(F);
     F.n = n;
     F.perm.assign(perm, perm + n);
-    std::vector<int32_t> col2chunk(n, -1);
+    F.col0.resize(nsuper);
+    F.cw.resize(nsuper);
+    F.nb.resize(nsuper);
+    F.tile_off.resize(nsuper);
+    F.row_off.resize(nsuper);
+    std::vector<int32_t> col2super(n, -1);
     std::vector<ConvTile> conv;
-    std::vector<double> linv, dinv;
-    int64_t tile_doubles = 0, nrows_tot = 0;
+    std::vector<double> aux;  // small supernodes: Linv and Dinv blocks; wide supernodes: device-side work space behind it
+    int64_t tile_doubles = 0, nrows_tot = 0, aux_wide = 0;
+    struct Wide {
+        int32_t J;
+        int64_t linv, dinv;  // offsets in aux (device)
+    };
+    std::vector<Wide> wide;
+    // pass 1: layout, row lists, small-supernode inverses on the host
     for (int32_t J = 0; J < nsuper; ++J) {
-        const int32_t f = super[J], l = super[J + 1], cw = l - f;
+        const int32_t f = super[J], cw = super[J + 1] - f;
+        const int64_t m = pi[J + 1] - pi[J];
+        const int32_t nb = (int32_t)(m - cw);
+        if (cw <= 0 || nb < 0) return fail("factor of subdomain %d: malformed supernode %d", sub, J);
+        F.col0[J] = f;
+        F.cw[J] = cw;
+        F.nb[J] = nb;
+        F.tile_off[J] = tile_doubles;
+        F.row_off[J] = nrows_tot;
+        F.nnz_lower += (int64_t)cw * (cw + 1) / 2 + (int64_t)nb * cw;
+        for (int32_t j = 0; j < cw; ++j) col2super[f + j] = J;
+        const int32_t Rd = (cw + 31) / 32, Rb = (nb + 31) / 32;
+        // row targets: diagonal rows are the supernode's own columns (in X), below rows its row structure (in W)
+        for (int32_t r = 0; r < Rd * 32; ++r) F.rows_host.push_back(r < cw ? -2 - (f + r) : -1);  // encoded: -2-k = X position k
+        for (int32_t r = 0; r < Rb * 32; ++r) F.rows_host.push_back(r < nb ? s[pi[J] + cw + r] : -1);
+        tile_doubles += (int64_t)(Rd + Rb) * 32 * cw;
+        nrows_tot += (int64_t)(Rd + Rb) * 32;
+    }
+    // aux layout: [small-supernode Linv | small-supernode Dinv | wide work space]
+    std::vector<int64_t> linv_off(nsuper, -1), dinv_off(nsuper, -1);
+    for (int32_t J = 0; J < nsuper; ++J) {
+        const int32_t cw = F.cw[J];
+        if (cw > 32) continue;
         const int64_t m = pi[J + 1] - pi[J];
         const double *Pn = x + px[J];
-        F.nnz_lower += (int64_t)cw * (cw + 1) / 2 + (m - cw) * cw;
-        for (int32_t c0 = 0; c0 < cw; c0 += 32) {
-            const int32_t w = std::min(32, cw - c0);
-            const int32_t K = (int32_t)F.col0.size();
-            const int64_t below = m - (c0 + w);
-            const int32_t nt = (int32_t)((below + 31) / 32);
-            F.col0.push_back(f + c0);
-            F.w.push_back(w);
-            F.ntiles.push_back(nt);
-            F.tile_off.push_back(tile_doubles);
-            F.row_off.push_back(nrows_tot);
-            F.dinv_off.push_back((int64_t)dinv.size());
-            for (int32_t j = 0; j < w; ++j) col2chunk[f + c0 + j] = K;
-            // rows below the chunk: rest of the supernode's columns, then its row structure
-            for (int64_t r = c0 + w; r < m; ++r) F.rows_host.push_back(r < cw ? f + (int32_t)r : s[pi[J] + r]);
-            for (int64_t r = below; r < (int64_t)nt * 32; ++r) F.rows_host.push_back(-1);
-            // L_KK^{-1} (lower, column-major) and Dinv = L_KK^{-T} L_KK^{-1}
-            const int64_t lo = (int64_t)linv.size();
-            linv.resize(lo + (size_t)w * w, 0.0);
-            double *Li = linv.data() + lo;
-            auto Lkk = [&](int a, int b) { return Pn[(int64_t)(c0 + b) * m + (c0 + a)]; };
-            for (int j = 0; j < w; ++j) {
-                const double djj = Lkk(j, j);
-                if (!(djj > 0.0)) return fail("factor of subdomain %d has a non-positive pivot", sub);
-                Li[(int64_t)j * w + j] = 1.0 / djj;
-                for (int i = j + 1; i < w; ++i) {
-                    double acc = 0.0;
-                    for (int k = j; k < i; ++k) acc += Lkk(i, k) * Li[(int64_t)j * w + k];
-                    Li[(int64_t)j * w + i] = -acc / Lkk(i, i);
-                }
+        const int64_t lo = (int64_t)aux.size();
+        aux.resize(lo + 2 * (size_t)cw * cw, 0.0);
+        double *Li = aux.data() + lo, *Di = Li + (size_t)cw * cw;
+        linv_off[J] = lo;
+        dinv_off[J] = lo + (int64_t)cw * cw;
+        auto Lkk = [&](int a, int b) { return Pn[(int64_t)b * m + a]; };
+        for (int j = 0; j < cw; ++j) {
+            const double djj = Lkk(j, j);
+            if (!(djj > 0.0)) return fail("factor of subdomain %d has a non-positive pivot", sub);
+            Li[(int64_t)j * cw + j] = 1.0 / djj;
+            for (int i = j + 1; i < cw; ++i) {
+                double acc = 0.0;
+                for (int k = j; k < i; ++k) acc += Lkk(i, k) * Li[(int64_t)j * cw + k];
+                Li[(int64_t)j * cw + i] = -acc / Lkk(i, i);
             }
-            const size_t d0 = dinv.size();
-            dinv.resize(d0 + (size_t)w * w);
-            for (int a = 0; a < w; ++a)
-                for (int b = 0; b <= a; ++b) {
-                    double acc = 0.0;
-                    for (int k = a; k < w; ++k) acc += Li[(int64_t)a * w + k] * Li[(int64_t)b * w + k];
-                    dinv[d0 + (size_t)b * w + a] = acc;
-                    dinv[d0 + (size_t)a * w + b] = acc;
-                }
-            for (int32_t t = 0; t < nt; ++t) {
+        }
+        for (int a = 0; a < cw; ++a)
+            for (int b = 0; b <= a; ++b) {
+                double acc = 0.0;
+                for (int k = a; k < cw; ++k) acc += Li[(int64_t)a * cw + k] * Li[(int64_t)b * cw + k];
+                Di[(size_t)b * cw + a] = acc;
+                Di[(size_t)a * cw + b] = acc;
+            }
+    }
+    const int64_t aux_small = (int64_t)aux.size();
+    for (int32_t J = 0; J < nsuper; ++J) {
+        const int32_t cw = F.cw[J];
+        if (cw <= 32) continue;
+        Wide wd;
+        wd.J = J;
+        wd.linv = aux_small + aux_wide;
+        wd.dinv = wd.linv + (int64_t)cw * cw;
+        aux_wide += 2 * (int64_t)cw * cw;
+        linv_off[J] = wd.linv;
+        dinv_off[J] = wd.dinv;
+        wide.push_back(wd);
+    }
+    // conversion list
+    for (int32_t J = 0; J < nsuper; ++J) {
+        const int32_t cw = F.cw[J], nb = F.nb[J];
+        const int64_t m = pi[J + 1] - pi[J];
+        const int32_t Rd = (cw + 31) / 32, Rb = (nb + 31) / 32, ncc = (cw + 31) / 32;
+        for (int32_t r = 0; r < Rd + Rb; ++r)
+            for (int32_t cc = 0; cc < ncc; ++cc) {
                 ConvTile ct;
-                ct.src = px[J] + (int64_t)c0 * m + (c0 + w) + (int64_t)t * 32;
-                ct.dst = tile_doubles + (int64_t)t * 32 * w;
-                ct.linv = lo;
-                ct.ld = (int32_t)m;
-                ct.nrows = (int32_t)std::min<int64_t>(32, below - (int64_t)t * 32);
-                ct.w = w;
-                ct.pad = 0;
+                ct.w = (int16_t)std::min(32, cw - cc * 32);
+                ct.dst = F.tile_off[J] + (int64_t)r * 32 * cw + (int64_t)cc * 1024;
+                ct.linv = 0;
+                if (r < Rd) {  // inverse diagonal block, full symmetric
+                    ct.kind = 1;
+                    ct.srcsel = 1;
+                    ct.ld = cw;
+                    ct.src = dinv_off[J] + (int64_t)cc * 32 * cw + (int64_t)r * 32;
+                    ct.nrows = std::min(32, cw - r * 32);
+                } else {
+                    const int32_t rb = r - Rd;
+                    ct.srcsel = 0;
+                    ct.ld = (int32_t)m;
+                    ct.src = px[J] + (int64_t)cc * 32 * m + cw + (int64_t)rb * 32;
+                    ct.nrows = std::min(32, nb - rb * 32);
+                    if (cw <= 32) {
+                        ct.kind = 0;
+                        ct.linv = linv_off[J];
+                    } else
+                        ct.kind = 1;  // the raw panel already holds -Lt after the cuBLAS pass
+                }
                 conv.push_back(ct);
             }
-            tile_doubles += (int64_t)nt * 32 * w;
-            nrows_tot += (int64_t)nt * 32;
-        }
     }
-    const int32_t nch = (int32_t)F.col0.size();
-    F.parent.assign(nch, -1);
-    F.level.assign(nch, 0);
-    for (int32_t K = 0; K < nch; ++K) {
-        if (F.ntiles[K] > 0) {
-            const int32_t r0 = F.rows_host[F.row_off[K]];
-            F.parent[K] = col2chunk[r0];
-            if (F.parent[K] <= K) return fail("factor of subdomain %d is not in elimination order", sub);
+    // parents and levels (supernodal elimination tree)
+    F.parent.assign(nsuper, -1);
+    F.level.assign(nsuper, 0);
+    for (int32_t J = 0; J < nsuper; ++J)
+        if (F.nb[J] > 0) {
+            F.parent[J] = col2super[s[pi[J] + F.cw[J]]];
+            if (F.parent[J] <= J) return fail("factor of subdomain %d is not in elimination order", sub);
         }
-    }
-    for (int32_t K = 0; K < nch; ++K)
-        if (F.parent[K] >= 0) F.level[F.parent[K]] = std::max(F.level[F.parent[K]], F.level[K] + 1);
+    for (int32_t J = 0; J < nsuper; ++J)
+        if (F.parent[J] >= 0) F.level[F.parent[J]] = std::max(F.level[F.parent[J]], F.level[J] + 1);
     F.panel_doubles = tile_doubles;
-    // device: raw panels (temporary) -> Lt tiles
-    double *raw = nullptr, *dlinv = nullptr;
+    // device: raw panels + aux -> tiles
+    double *raw = nullptr, *daux = nullptr;
     ConvTile *dconv = nullptr;
     CK(dev_upload(&raw, x, (size_t)px[nsuper]));
-    CK(dev_upload(&dlinv, linv.data(), linv.size()));
+    CU(cudaMalloc((void **)&daux, sizeof(double) * std::max<int64_t>(1, aux_small + aux_wide)));
+    if (aux_small) CU(cudaMemcpy(daux, aux.data(), sizeof(double) * aux_small, cudaMemcpyHostToDevice));
+    if (!wide.empty()) {
+        if (!c->blas) {
+            if (cublasCreate(&c->blas) != CUBLAS_STATUS_SUCCESS) return fail("cublasCreate failed");
+            cublasSetStream(c->blas, c->s);
+        }
+        CU(cudaMemsetAsync(daux + aux_small, 0, sizeof(double) * aux_wide, c->s));
+        const double one = 1.0, zero = 0.0, mone = -1.0;
+        for (const Wide &wd : wide) {
+            const int32_t cw = F.cw[wd.J], nb = F.nb[wd.J];
+            const int64_t m = pi[wd.J + 1] - pi[wd.J];
+            double *L11 = raw + px[wd.J], *Li = daux + wd.linv, *Di = daux + wd.dinv;
+            // Linv = L11^{-1}: solve L11 * Linv = I
+            LAUNCH(c, set_identity_kernel, nblocks(cw), 256, cw, Li);
+            if (cublasDtrsm(c->blas, CUBLAS_SIDE_LEFT, CUBLAS_FILL_MODE_LOWER, CUBLAS_OP_N, CUBLAS_DIAG_NON_UNIT, cw, cw, &one, L11, (int)m, Li, cw) != CUBLAS_STATUS_SUCCESS)
+                return fail("cublasDtrsm (Linv) failed");
+            // Dinv = Linv^T Linv
+            if (cublasDgemm(c->blas, CUBLAS_OP_T, CUBLAS_OP_N, cw, cw, cw, &one, Li, cw, Li, cw, &zero, Di, cw) != CUBLAS_STATUS_SUCCESS)
+                return fail("cublasDgemm (Dinv) failed");
+            // below panel <- -L_below L11^{-1}: solve X * L11 = -L_below in place
+            if (nb > 0 && cublasDtrsm(c->blas, CUBLAS_SIDE_RIGHT, CUBLAS_FILL_MODE_LOWER, CUBLAS_OP_N, CUBLAS_DIAG_NON_UNIT, nb, cw, &mone, L11, (int)m, L11 + cw, (int)m) != CUBLAS_STATUS_SUCCESS)
+                return fail("cublasDtrsm (Lt) failed");
+        }
+    }
     CK(dev_upload(&dconv, conv.data(), conv.size()));
-    CK(dev_upload(&F.dinv, dinv.data(), dinv.size()));
     CU(cudaMalloc((void **)&F.panel, sizeof(double) * std::max<int64_t>(1, tile_doubles)));
     if (!conv.empty()) {
         const int64_t nt = (int64_t)conv.size();
-        LAUNCH(c, convert_tiles_kernel, nblocks(nt * 32), 256, nt, dconv, raw, dlinv, F.panel);
+        LAUNCH(c, convert_tiles_kernel, nblocks(nt * 32), 256, nt, dconv, raw, daux, F.panel);
     }
     CU(cudaStreamSynchronize(c->s));
     CU(cudaGetLastError());
     cudaFree(raw);
-    cudaFree(dlinv);
+    cudaFree(daux);
     cudaFree(dconv);
     F.present = true;
     c->finalized = false;
@@ -593,8 +667,8 @@ extern "C" int ddm_finalize(ddm_ctx *c)
     for (int32_t i = 0; i < c->nsub; ++i)
         if (!c->fac[i].present) return fail("no factor uploaded for subdomain %d", i);
     // release an earlier schedule
-    void *old[] = {c->gidx, c->pouP, c->Zp, c->W, c->X, c->zoff, c->d_sub_n, c->d_sub_k, c->d_koff, c->seg_ptr, c->segs,
-                   c->cpartial, c->dptr, c->dpos, c->fwd_tasks, c->bwd_tasks, c->need, c->nslices, c->cnt};
+    void *old[] = {c->gidx, c->pouP, c->Zp, c->W, c->zoff, c->d_sub_n, c->d_sub_k, c->d_koff, c->seg_ptr, c->segs,
+                   c->cpartial, c->dptr, c->dpos, c->fwd_tasks, c->bwd_tasks, c->cnt};
     for (void *p : old) cudaFree(p);
 
     const int32_t ns = c->nsub;
@@ -616,8 +690,9 @@ extern "C" int ddm_finalize(ddm_ctx *c)
     CK(dev_upload(&c->gidx, gidx.data(), gidx.size()));
     if (c->have_pou) CK(dev_upload(&c->pouP, pouP.data(), pouP.size()));
     else c->pouP = nullptr;
-    CU(cudaMalloc((void **)&c->W, sizeof(double) * std::max<int64_t>(1, P)));
-    CU(cudaMalloc((void **)&c->X, sizeof(double) * std::max<int64_t>(1, P)));
+    if (2 * P >= (int64_t)INT32_MAX) return fail("too many subdomain positions for one GPU");
+    CU(cudaMalloc((void **)&c->W, sizeof(double) * std::max<int64_t>(1, 2 * P)));  // WX: W = [0,P), X = [P,2P)
+    c->X = c->W + P;
     // coarse basis permuted to pivot order (column-major per subdomain)
     c->koff.assign(ns + 1, 0);
     std::vector<int64_t> zoff(ns + 1, 0);
@@ -666,85 +741,116 @@ extern "C" int ddm_finalize(ddm_ctx *c)
         CK(dev_upload(&c->dptr, dptr.data(), dptr.size()));
         CK(dev_upload(&c->dpos, dpos.data(), dpos.size()));
     }
-    // triangular-solve schedules
-    std::vector<int32_t> chunk_base(ns + 1, 0);
-    for (int32_t i = 0; i < ns; ++i) chunk_base[i + 1] = chunk_base[i] + (int32_t)c->fac[i].col0.size();
-    c->nchunks = chunk_base[ns];
-    std::vector<int32_t> need(c->nchunks, 0), nslices(c->nchunks, 0);
+    // triangular-solve schedules (trisolve.cuh): tasks in elimination-tree level order over all subdomains
+    std::vector<int32_t> sn_base(ns + 1, 0);
+    for (int32_t i = 0; i < ns; ++i) sn_base[i + 1] = sn_base[i] + (int32_t)c->fac[i].cw.size();
+    c->nsn = sn_base[ns];
+    std::vector<int32_t> need(c->nsn, 0), nbwd(c->nsn, 0);
     struct Key {
-        int32_t level;
-        int32_t sub, chunk, slice;
+        int32_t level, sub, J, kind /* 0 below, 1 diag (fwd) */, a, b;  // fwd: row tile a, chunk group b; bwd: chunk a, row group b
     };
-    std::vector<Key> keys;
-    const int tpt = c->tpt;
-    double bytes_f = 0, bytes_alg = 0;
+    std::vector<Key> fkeys, bkeys;
+    double bytes_stored = 0, bytes_alg = 0, bytes_below = 0;
     for (int32_t i = 0; i < ns; ++i) {
         SubFactor &F = c->fac[i];
         const int64_t o = c->sub_ptr[i];
-        // absolute row offsets
         std::vector<int32_t> rabs(F.rows_host.size());
-        for (size_t q = 0; q < rabs.size(); ++q) rabs[q] = F.rows_host[q] < 0 ? -1 : (int32_t)(o + F.rows_host[q]);
+        for (size_t q = 0; q < rabs.size(); ++q) {
+            const int32_t v = F.rows_host[q];
+            rabs[q] = v == -1 ? -1 : v <= -2 ? (int32_t)(P + o + (-2 - v)) : (int32_t)(o + v);
+        }
         cudaFree(F.rowidx);
         F.rowidx = nullptr;
         CK(dev_upload(&F.rowidx, rabs.data(), rabs.size()));
-        for (int32_t K = 0; K < (int32_t)F.col0.size(); ++K) {
-            const int32_t nsl = std::max(1, (F.ntiles[K] + tpt - 1) / tpt);
-            nslices[chunk_base[i] + K] = F.ntiles[K] > 0 ? nsl : 0;
-            if (F.parent[K] >= 0) need[chunk_base[i] + F.parent[K]] += nsl;
-            for (int32_t sl = 0; sl < nsl; ++sl) keys.push_back({F.level[K], i, K, sl});
+        const int32_t nsn = (int32_t)F.cw.size();
+        for (int32_t J = 0; J < nsn; ++J) {
+            const int32_t cw = F.cw[J], nb = F.nb[J];
+            const int32_t Rd = (cw + 31) / 32, Rb = (nb + 31) / 32, ncc = (cw + 31) / 32;
+            const int32_t ngc = (ncc + kGroup - 1) / kGroup, ngr = (Rb + kGroup - 1) / kGroup;
+            for (int32_t r = 0; r < Rb; ++r)
+                for (int32_t g = 0; g < ngc; ++g) fkeys.push_back({F.level[J], i, J, 0, Rd + r, g});
+            for (int32_t r = 0; r < Rd; ++r)
+                for (int32_t g = 0; g < ngc; ++g) fkeys.push_back({F.level[J], i, J, 1, r, g});
+            if (F.parent[J] >= 0) need[sn_base[i] + F.parent[J]] += Rb * ngc;
+            for (int32_t cc = 0; cc < ncc; ++cc)
+                for (int32_t g = 0; g < ngr; ++g) bkeys.push_back({F.level[J], i, J, 0, cc, g});
+            nbwd[sn_base[i] + J] = ncc * ngr;
+            bytes_below += 8.0 * (double)Rb * 32 * cw;
         }
-        bytes_f += 8.0 * F.panel_doubles + 4.0 * F.rows_host.size();
+        bytes_stored += 8.0 * F.panel_doubles + 4.0 * F.rows_host.size();
         bytes_alg += 8.0 * F.nnz_lower;
     }
-    auto make_task = [&](const Key &k) {
-        const SubFactor &F = c->fac[k.sub];
-        TriTask t;
-        const int32_t t0 = k.slice * tpt;
-        const int32_t nt = std::max(0, std::min(tpt, F.ntiles[k.chunk] - t0));
-        t.panel = F.panel + F.tile_off[k.chunk] + (int64_t)t0 * 32 * F.w[k.chunk];
-        t.rowidx = F.rowidx + F.row_off[k.chunk] + (int64_t)t0 * 32;
-        t.dinv = F.dinv + F.dinv_off[k.chunk];
-        t.col_abs = (int32_t)(c->sub_ptr[k.sub] + F.col0[k.chunk]);
-        t.chunk = chunk_base[k.sub] + k.chunk;
-        t.parent = F.parent[k.chunk] >= 0 ? chunk_base[k.sub] + F.parent[k.chunk] : -1;
-        t.w = (int16_t)F.w[k.chunk];
-        t.ntiles = (int16_t)nt;
-        t.first = k.slice == 0;
-        t.pad = 0;
-        return t;
-    };
-    std::stable_sort(keys.begin(), keys.end(), [](const Key &a, const Key &b) { return a.level < b.level; });
+    // forward: ascending level, below-row tasks (they release the parent) before diagonal tasks of the same level
+    std::stable_sort(fkeys.begin(), fkeys.end(), [](const Key &a, const Key &b) { return a.level != b.level ? a.level < b.level : a.kind < b.kind; });
+    std::stable_sort(bkeys.begin(), bkeys.end(), [](const Key &a, const Key &b) { return a.level > b.level; });
     std::vector<TriTask> fwd, bwd;
-    fwd.reserve(keys.size());
-    for (const Key &k : keys) fwd.push_back(make_task(k));
-    for (auto it = keys.rbegin(); it != keys.rend(); ++it) {
-        TriTask t = make_task(*it);
-        if (t.ntiles > 0) bwd.push_back(t);
+    fwd.reserve(fkeys.size());
+    bwd.reserve(bkeys.size());
+    for (const Key &k : fkeys) {
+        const SubFactor &F = c->fac[k.sub];
+        const int32_t cw = F.cw[k.J], ncc = (cw + 31) / 32;
+        const int32_t c0 = k.b * kGroup, c1 = std::min(ncc, c0 + kGroup);
+        TriTask t;
+        t.tiles = F.panel + F.tile_off[k.J] + (int64_t)k.a * 32 * cw + (int64_t)c0 * 1024;
+        t.rowidx = F.rowidx + F.row_off[k.J] + (int64_t)k.a * 32;
+        t.vec = (int32_t)(c->sub_ptr[k.sub] + F.col0[k.J] + c0 * 32);
+        t.stride = 1024;
+        t.ntiles = (int16_t)(c1 - c0);
+        t.w = 32;
+        t.wlast = (int16_t)std::min(32, cw - (c1 - 1) * 32);
+        t.signal_on = (k.kind == 0 && F.parent[k.J] >= 0) ? 1 : 0;
+        t.wait_cnt = need[sn_base[k.sub] + k.J] > 0 ? sn_base[k.sub] + k.J : -1;
+        t.wait_need = need[sn_base[k.sub] + k.J];
+        t.signal_cnt = F.parent[k.J] >= 0 ? sn_base[k.sub] + F.parent[k.J] : 0;
+        t.pad = 0;
+        fwd.push_back(t);
+    }
+    for (const Key &k : bkeys) {
+        const SubFactor &F = c->fac[k.sub];
+        const int32_t cw = F.cw[k.J], nb = F.nb[k.J];
+        const int32_t Rd = (cw + 31) / 32, Rb = (nb + 31) / 32;
+        const int32_t r0 = k.b * kGroup, r1 = std::min(Rb, r0 + kGroup);
+        const int32_t par = sn_base[k.sub] + F.parent[k.J];
+        TriTask t;
+        t.tiles = F.panel + F.tile_off[k.J] + (int64_t)(Rd + r0) * 32 * cw + (int64_t)k.a * 1024;
+        t.rowidx = F.rowidx + F.row_off[k.J] + (int64_t)(Rd + r0) * 32;
+        t.vec = (int32_t)(P + c->sub_ptr[k.sub] + F.col0[k.J] + k.a * 32);
+        t.stride = 32 * cw;
+        t.ntiles = (int16_t)(r1 - r0);
+        t.w = t.wlast = (int16_t)std::min(32, cw - k.a * 32);
+        t.signal_on = 1;
+        t.wait_cnt = nbwd[par] > 0 ? c->nsn + par : -1;
+        t.wait_need = nbwd[par];
+        t.signal_cnt = c->nsn + sn_base[k.sub] + k.J;
+        t.pad = 0;
+        bwd.push_back(t);
     }
     c->n_fwd = (int32_t)fwd.size();
     c->n_bwd = (int32_t)bwd.size();
     CK(dev_upload(&c->fwd_tasks, fwd.data(), fwd.size()));
     CK(dev_upload(&c->bwd_tasks, bwd.data(), bwd.size()));
-    CK(dev_upload(&c->need, need.data(), need.size()));
-    CK(dev_upload(&c->nslices, nslices.data(), nslices.size()));
-    CU(cudaMalloc((void **)&c->cnt, sizeof(int) * (2 * (size_t)c->nchunks + 2)));
+    CU(cudaMalloc((void **)&c->cnt, sizeof(int) * (2 * (size_t)c->nsn + 2)));
+    CU(cudaFuncSetAttribute(trisolve_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kTriSmemBytes));
+    CU(cudaFuncSetAttribute(trisolve_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kTriSmemBytes));
     int bps_f = 0, bps_b = 0;
-    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps_f, trisolve_fwd_kernel, 256, 0));
-    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps_b, trisolve_bwd_kernel, 256, 0));
-    c->tri_grid = std::max(1, std::min(bps_f, bps_b)) * c->sm_count;
-    if (const char *e = getenv("DDM_TRI_BLOCKS_PER_SM")) c->tri_grid = std::max(1, std::min(atoi(e), std::min(bps_f, bps_b))) * c->sm_count;
+    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps_f, trisolve_fwd_kernel, kTriWarps * 32, kTriSmemBytes));
+    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps_b, trisolve_bwd_kernel, kTriWarps * 32, kTriSmemBytes));
+    if (bps_f < 1 || bps_b < 1) return fail("triangular-solve kernels do not fit on this device (needs %zu bytes of shared memory per CTA)", kTriSmemBytes);
+    c->tri_grid = c->sm_count;
     // algorithmic bytes
     double zbytes = 0;
     for (int32_t i = 0; i < ns; ++i) zbytes += 8.0 * c->sub_k[i] * sub_n[i];
     c->stats["restrict"] = 20.0 * P;
     c->stats["trisolve_fwd"] = bytes_alg + 16.0 * P;
     c->stats["trisolve_bwd"] = bytes_alg + 16.0 * P;
-    c->stats["trisolve_stored"] = bytes_f;
+    c->stats["trisolve_stored"] = bytes_stored;            // forward sweep reads all of it
+    c->stats["trisolve_stored_bwd"] = bytes_below;         // backward sweep reads the below panels only
     c->stats["prolong"] = 20.0 * P + 16.0 * c->nloc;
     c->stats["coarse"] = 2.0 * zbytes + 8.0 * (double)c->N0 * c->N0;
     c->stats["factor_nnz"] = bytes_alg / 8.0;
     c->stats["n_tasks_fwd"] = c->n_fwd;
-    c->stats["n_chunks"] = c->nchunks;
+    c->stats["n_tasks_bwd"] = c->n_bwd;
+    c->stats["n_supernodes"] = c->nsn;
     c->finalized = true;
     return 0;
 }
@@ -869,7 +975,7 @@ static int need_final(ddm_ctx *c)
 static int restrict_all(ddm_ctx *c, const double *d, int with_coarse)
 {
     ScopedTimer tm(c, "Schwarz/get defect");
-    LAUNCH(c, restrict_kernel, c->nseg, 256, c->segs, c->gidx, d, c->W, (double *)nullptr, with_coarse, c->zoff, c->d_sub_n,
+    LAUNCH(c, restrict_kernel, c->nseg, 256, c->segs, c->gidx, d, c->W, c->X, with_coarse, c->zoff, c->d_sub_n,
            c->d_sub_k, c->Zp, c->cpartial, c->kpad);
     return 0;
 }
@@ -892,18 +998,19 @@ static int coarse_solve(ddm_ctx *c)
 static int trisolve(ddm_ctx *c)
 {
     ScopedTimer tm(c, "Schwarz/local solve");
-    CU(cudaMemsetAsync(c->cnt, 0, sizeof(int) * (2 * (size_t)c->nchunks + 2), c->s));
-    int *cnt_f = c->cnt, *cnt_b = c->cnt + c->nchunks, *tick_f = c->cnt + 2 * c->nchunks, *tick_b = tick_f + 1;
+    CU(cudaMemsetAsync(c->cnt, 0, sizeof(int) * (2 * (size_t)c->nsn + 2), c->s));
+    int *cnt = c->cnt, *tick_f = c->cnt + 2 * c->nsn, *tick_b = tick_f + 1;
     {
         ScopedTimer tf(c, "Schwarz/local solve fwd");
-        void *args[] = {&c->fwd_tasks, &c->n_fwd, &c->W, &c->X, &c->need, &cnt_f, &tick_f};
-        CU(cudaLaunchCooperativeKernel((void *)trisolve_fwd_kernel, dim3(c->tri_grid), dim3(256), args, 0, c->s));
+        void *args[] = {&c->fwd_tasks, &c->n_fwd, &c->W, &cnt, &tick_f};
+        CU(cudaLaunchCooperativeKernel((void *)trisolve_fwd_kernel, dim3(c->tri_grid), dim3(kTriWarps * 32), args, kTriSmemBytes, c->s));
         c->launches++;
     }
     if (c->n_bwd > 0) {
         ScopedTimer tb(c, "Schwarz/local solve bwd");
-        void *args[] = {&c->bwd_tasks, &c->n_bwd, &c->X, &c->nslices, &cnt_b, &tick_b};
-        CU(cudaLaunchCooperativeKernel((void *)trisolve_bwd_kernel, dim3(c->tri_grid), dim3(256), args, 0, c->s));
+        int xoff = (int)c->P;
+        void *args[] = {&c->bwd_tasks, &c->n_bwd, &c->W, &cnt, &tick_b, &xoff};
+        CU(cudaLaunchCooperativeKernel((void *)trisolve_bwd_kernel, dim3(c->tri_grid), dim3(kTriWarps * 32), args, kTriSmemBytes, c->s));
         c->launches++;
     }
     return 0;

@@ -264,195 +264,5 @@ __global__ void __launch_bounds__(256) gather_sum_kernel(int64_t nloc, const int
     x[v] = accumulate ? x[v] + acc : acc;
 }
 
-// ------------------------------------------------------------------------------------------------
-// K3  batched subdomain solves  x_i = A_i^{-1} d_i  for all hosted subdomains in two persistent kernels.
-//
-// Replaces Dune::Cholmod::apply -> cholmod_l_solve (extern/dune-istl/dune/istl/cholmod.hh:263-306).
-// At upload the supernodal LL^T factor is re-expressed as a block LDL^T with column chunks of width
-// w <= 32:  A = Lt D Lt^T, Lt unit block lower triangular (Lt_below = L_below L_KK^{-1}) and
-// D_K = L_KK L_KK^T stored as its explicit inverse.  With that form no triangular solve is left:
-//   forward : for chunk K in tree order   y_below -= Lt_below y_K          (scatter, RED.F64)
-//   diagonal: z_K = Dinv_K y_K                                              (fused into forward)
-//   backward: for chunk K in reverse      x_K = z_K - Lt_below^T x_below    (gather + warp transpose-reduce)
-// The panels are stored as tiles of 32 rows x w columns, column-major inside the tile, so lane i of a
-// warp owns row i and every load instruction reads 256 contiguous bytes.  Work is cut into tasks
-// (a chunk's run of <= tpt tiles) listed in elimination-tree level order over ALL subdomains; warps
-// take tasks from a ticket counter and synchronise point-to-point through per-chunk counters
-// (a task waits only for tasks with smaller ticket numbers, so the persistent grid cannot deadlock
-// as long as it is co-resident -- it is launched cooperatively).
-// ------------------------------------------------------------------------------------------------
-struct TriTask {
-    const double *panel;   // first tile of the task
-    const int32_t *rowidx; // row offsets into W/X for the task's tiles (-1 = padding)
-    const double *dinv;    // chunk's w x w inverse diagonal block (column-major)
-    int32_t col_abs;       // offset of the chunk's first column in W/X
-    int32_t chunk;         // global chunk id
-    int32_t parent;        // global chunk id of the parent chunk, -1 for a root
-    int16_t w;
-    int16_t ntiles;
-    int32_t first;         // 1 if this task is the first slice of its chunk (does the diagonal step)
-    int32_t pad;
-};
-
-__device__ __forceinline__ int ld_acquire(const int *p)
-{
-    int v;
-    asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-    return v;
-}
-
-__device__ __forceinline__ void wait_counter(const int *cnt, int need, int lane)
-{
-    if (need > 0) {
-        if (lane == 0) {
-            while (ld_acquire(cnt) < need) __nanosleep(40);
-        }
-        __syncwarp();
-    }
-}
-
-// Loads one half-tile (16 columns x 32 rows): 16 independent 256-byte warp loads.
-__device__ __forceinline__ void load_half(double (&pv)[16], const double *P, int w, int h, int lane)
-{
-#pragma unroll
-    for (int j = 0; j < 16; ++j) pv[j] = (h * 16 + j < w) ? __ldcs(P + (h * 16 + j) * 32 + lane) : 0.0;
-}
-
-__global__ void __launch_bounds__(256, 2) trisolve_fwd_kernel(const TriTask *__restrict__ tasks, int ntasks, double *W,
-                                                              double *X, const int32_t *__restrict__ need, int *cnt,
-                                                              int *ticket)
-{
-    const int lane = threadIdx.x & 31;
-    for (;;) {
-        int t = 0;
-        if (lane == 0) t = atomicAdd(ticket, 1);
-        t = __shfl_sync(kFull, t, 0);
-        if (t >= ntasks) break;
-        const TriTask tk = tasks[t];
-        const int w = tk.w;
-        const int nh = tk.ntiles * 2; // half-tiles
-        // the first half-tile is fetched before the dependency wait: its latency overlaps the wait
-        double pv[16];
-        if (nh > 0) load_half(pv, tk.panel, w, 0, lane);
-        wait_counter(cnt + tk.chunk, need[tk.chunk], lane);
-        const double yl = (lane < w) ? __ldcg(W + tk.col_abs + lane) : 0.0;
-        double yv[32];
-#pragma unroll
-        for (int j = 0; j < 32; ++j) yv[j] = __shfl_sync(kFull, yl, j);
-        if (tk.first) {
-            double z = 0.0;
-#pragma unroll
-            for (int j = 0; j < 32; ++j)
-                if (j < w && lane < w) z = fma(__ldg(tk.dinv + j * w + lane), yv[j], z);
-            if (lane < w) X[tk.col_abs + lane] = z;
-        }
-        double acc = 0.0;
-        for (int hh = 0; hh < nh; ++hh) {
-            if (hh & 1) {
-#pragma unroll
-                for (int j = 0; j < 16; ++j) acc = fma(pv[j], yv[16 + j], acc);
-            } else {
-#pragma unroll
-                for (int j = 0; j < 16; ++j) acc = fma(pv[j], yv[j], acc);
-            }
-            if (hh + 1 < nh) load_half(pv, tk.panel + (int64_t)((hh + 1) >> 1) * 32 * w, w, (hh + 1) & 1, lane);
-            if (hh & 1) {
-                const int r = __ldg(tk.rowidx + (hh >> 1) * 32 + lane);
-                if (r >= 0) atomicAdd(W + r, -acc);
-                acc = 0.0;
-            }
-        }
-        __threadfence();
-        __syncwarp();
-        if (lane == 0 && tk.parent >= 0) atomicAdd(cnt + tk.parent, 1);
-    }
-}
-
-__global__ void __launch_bounds__(256, 2) trisolve_bwd_kernel(const TriTask *__restrict__ tasks, int ntasks, double *X,
-                                                              const int32_t *__restrict__ nslices, int *cnt, int *ticket)
-{
-    const int lane = threadIdx.x & 31;
-    for (;;) {
-        int t = 0;
-        if (lane == 0) t = atomicAdd(ticket, 1);
-        t = __shfl_sync(kFull, t, 0);
-        if (t >= ntasks) break;
-        const TriTask tk = tasks[t];
-        const int w = tk.w;
-        const int nh = tk.ntiles * 2;
-        double pv[16];
-        load_half(pv, tk.panel, w, 0, lane);
-        int r = __ldg(tk.rowidx + lane);
-        if (tk.parent >= 0) wait_counter(cnt + tk.parent, nslices[tk.parent], lane);
-        double acc[32];
-#pragma unroll
-        for (int j = 0; j < 32; ++j) acc[j] = 0.0;
-        double xr = (r >= 0) ? __ldcg(X + r) : 0.0;
-        for (int hh = 0; hh < nh; ++hh) {
-            if (hh & 1) {
-#pragma unroll
-                for (int j = 0; j < 16; ++j) acc[16 + j] = fma(pv[j], xr, acc[16 + j]);
-            } else {
-#pragma unroll
-                for (int j = 0; j < 16; ++j) acc[j] = fma(pv[j], xr, acc[j]);
-            }
-            if (hh + 1 < nh) {
-                load_half(pv, tk.panel + (int64_t)((hh + 1) >> 1) * 32 * w, w, (hh + 1) & 1, lane);
-                if (hh & 1) {
-                    r = __ldg(tk.rowidx + ((hh + 1) >> 1) * 32 + lane);
-                    xr = (r >= 0) ? __ldcg(X + r) : 0.0;
-                }
-            }
-        }
-        // transpose-reduce: afterwards lane L holds sum over lanes of acc[L]
-#pragma unroll
-        for (int half = 16; half >= 1; half >>= 1) {
-            const bool upper = (lane & half) != 0;
-#pragma unroll
-            for (int k = 0; k < half; ++k) {
-                const double send = upper ? acc[k] : acc[k + half];
-                const double keep = upper ? acc[k + half] : acc[k];
-                acc[k] = keep + __shfl_xor_sync(kFull, send, half);
-            }
-        }
-        if (lane < w) atomicAdd(X + tk.col_abs + lane, -acc[0]);
-        __threadfence();
-        __syncwarp();
-        if (lane == 0) atomicAdd(cnt + tk.chunk, 1);
-    }
-}
-
-// Setup-time conversion of raw supernodal panels (cholmod layout) into Lt tiles: one warp per tile.
-struct ConvTile {
-    int64_t src;    // offset in raw x of element (first row of tile, first column of chunk)
-    int64_t dst;    // offset in the tile array
-    int64_t linv;   // offset of the chunk's L_KK^{-1} (w x w, column-major, lower)
-    int32_t ld;     // leading dimension (rows) of the raw panel
-    int32_t nrows;  // valid rows in this tile (<= 32)
-    int32_t w;
-    int32_t pad;
-};
-
-__global__ void __launch_bounds__(256) convert_tiles_kernel(int64_t ntiles, const ConvTile *__restrict__ tiles,
-                                                            const double *__restrict__ raw, const double *__restrict__ linv,
-                                                            double *__restrict__ out)
-{
-    const int64_t t = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    const int lane = threadIdx.x & 31;
-    if (t >= ntiles) return;
-    const ConvTile ct = tiles[t];
-    const int w = ct.w;
-    double p[32];
-#pragma unroll
-    for (int k = 0; k < 32; ++k) p[k] = (k < w && lane < ct.nrows) ? raw[ct.src + (int64_t)k * ct.ld + lane] : 0.0;
-    const double *Li = linv + ct.linv;
-    for (int j = 0; j < w; ++j) {
-        double acc = 0.0;
-#pragma unroll
-        for (int k = 0; k < 32; ++k)
-            if (k >= j && k < w) acc = fma(p[k], __ldg(Li + (int64_t)j * w + k), acc);
-        out[ct.dst + (int64_t)j * 32 + lane] = acc;
-    }
-}
 
 } // namespace ddm

@@ -173,7 +173,7 @@ def test_cg_dropin_and_device_loops(case, with_coarse):
     assert rel(x.download(), xo) <= 1e-8 * max(1.0, np.linalg.cond(P.A.toarray()) * 1e-8)
     m = min(len(histo), len(r1.history))
     # identical recurrences; rounding differences grow along the CG iteration (cond(A) ~ 1e7)
-    assert np.allclose(r1.history[:5], histo[:5], rtol=1e-9) and np.allclose(r1.history[: m - 2], histo[: m - 2], rtol=1e-2)
+    assert np.allclose(r1.history[:5], histo[:5], rtol=1e-9) and np.allclose(r1.history[: min(m, 12)], histo[: min(m, 12)], rtol=1e-5)
     # device-resident loop (ddm_pcg_solve) and the host-buffer entry
     x, b = ctx.vector(np.zeros(P.n)), ctx.vector(P.b)
     r2 = cg.solve_device(x, b)
