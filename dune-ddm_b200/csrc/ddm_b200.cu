@@ -766,12 +766,17 @@ extern "C" int ddm_finalize(ddm_ctx *c)
         for (int32_t J = 0; J < nsn; ++J) {
             const int32_t cw = F.cw[J], nb = F.nb[J];
             const int32_t Rd = (cw + 31) / 32, Rb = (nb + 31) / 32, ncc = (cw + 31) / 32;
-            const int32_t ngc = (ncc + kGroup - 1) / kGroup, ngr = (Rb + kGroup - 1) / kGroup;
-            for (int32_t r = 0; r < Rb; ++r)
-                for (int32_t g = 0; g < ngc; ++g) fkeys.push_back({F.level[J], i, J, 0, Rd + r, g});
-            for (int32_t r = 0; r < Rd; ++r)
-                for (int32_t g = 0; g < ngc; ++g) fkeys.push_back({F.level[J], i, J, 1, r, g});
-            if (F.parent[J] >= 0) need[sn_base[i] + F.parent[J]] += Rb * ngc;
+            const int32_t ngr = (Rb + kGroup - 1) / kGroup;
+            int32_t nf = 0;
+            if (ncc >= kGroup) {  // wide: one row tile x a group of chunks
+                const int32_t ngc = (ncc + kGroup - 1) / kGroup;
+                for (int32_t r = 0; r < Rd + Rb; ++r)
+                    for (int32_t g = 0; g < ngc; ++g, ++nf) fkeys.push_back({F.level[J], i, J, r < Rd ? 1 : 0, r, g});
+            } else {  // narrow: several whole row tiles per task
+                const int32_t rpt = kGroup / ncc;
+                for (int32_t r = 0; r < Rd + Rb; r += rpt, ++nf) fkeys.push_back({F.level[J], i, J, 2, r, std::min(rpt, Rd + Rb - r)});
+            }
+            if (F.parent[J] >= 0) need[sn_base[i] + F.parent[J]] += nf;
             for (int32_t cc = 0; cc < ncc; ++cc)
                 for (int32_t g = 0; g < ngr; ++g) bkeys.push_back({F.level[J], i, J, 0, cc, g});
             nbwd[sn_base[i] + J] = ncc * ngr;
@@ -781,7 +786,7 @@ extern "C" int ddm_finalize(ddm_ctx *c)
         bytes_alg += 8.0 * F.nnz_lower;
     }
     // forward: ascending level, below-row tasks (they release the parent) before diagonal tasks of the same level
-    std::stable_sort(fkeys.begin(), fkeys.end(), [](const Key &a, const Key &b) { return a.level != b.level ? a.level < b.level : a.kind < b.kind; });
+    std::stable_sort(fkeys.begin(), fkeys.end(), [](const Key &a, const Key &b) { return a.level < b.level; });
     std::stable_sort(bkeys.begin(), bkeys.end(), [](const Key &a, const Key &b) { return a.level > b.level; });
     std::vector<TriTask> fwd, bwd;
     fwd.reserve(fkeys.size());
@@ -789,20 +794,25 @@ extern "C" int ddm_finalize(ddm_ctx *c)
     for (const Key &k : fkeys) {
         const SubFactor &F = c->fac[k.sub];
         const int32_t cw = F.cw[k.J], ncc = (cw + 31) / 32;
-        const int32_t c0 = k.b * kGroup, c1 = std::min(ncc, c0 + kGroup);
         TriTask t;
+        int32_t c0 = 0, c1 = ncc, nrt = 1;
+        if (k.kind == 2) nrt = k.b;
+        else {
+            c0 = k.b * kGroup;
+            c1 = std::min(ncc, c0 + kGroup);
+        }
         t.tiles = F.panel + F.tile_off[k.J] + (int64_t)k.a * 32 * cw + (int64_t)c0 * 1024;
         t.rowidx = F.rowidx + F.row_off[k.J] + (int64_t)k.a * 32;
         t.vec = (int32_t)(c->sub_ptr[k.sub] + F.col0[k.J] + c0 * 32);
         t.stride = 1024;
-        t.ntiles = (int16_t)(c1 - c0);
+        t.gstride = 32 * cw;
+        t.ncc = (int16_t)(c1 - c0);
+        t.ntiles = (int16_t)(nrt * (c1 - c0));
         t.w = 32;
         t.wlast = (int16_t)std::min(32, cw - (c1 - 1) * 32);
-        t.signal_on = (k.kind == 0 && F.parent[k.J] >= 0) ? 1 : 0;
         t.wait_cnt = need[sn_base[k.sub] + k.J] > 0 ? sn_base[k.sub] + k.J : -1;
         t.wait_need = need[sn_base[k.sub] + k.J];
-        t.signal_cnt = F.parent[k.J] >= 0 ? sn_base[k.sub] + F.parent[k.J] : 0;
-        t.pad = 0;
+        t.signal_cnt = F.parent[k.J] >= 0 ? sn_base[k.sub] + F.parent[k.J] : -1;
         fwd.push_back(t);
     }
     for (const Key &k : bkeys) {
@@ -816,13 +826,12 @@ extern "C" int ddm_finalize(ddm_ctx *c)
         t.rowidx = F.rowidx + F.row_off[k.J] + (int64_t)(Rd + r0) * 32;
         t.vec = (int32_t)(P + c->sub_ptr[k.sub] + F.col0[k.J] + k.a * 32);
         t.stride = 32 * cw;
-        t.ntiles = (int16_t)(r1 - r0);
+        t.gstride = 0;
+        t.ntiles = t.ncc = (int16_t)(r1 - r0);
         t.w = t.wlast = (int16_t)std::min(32, cw - k.a * 32);
-        t.signal_on = 1;
         t.wait_cnt = nbwd[par] > 0 ? c->nsn + par : -1;
         t.wait_need = nbwd[par];
         t.signal_cnt = c->nsn + sn_base[k.sub] + k.J;
-        t.pad = 0;
         bwd.push_back(t);
     }
     c->n_fwd = (int32_t)fwd.size();

@@ -18,7 +18,7 @@
 // (cp.async.bulk, global -> shared, completion on an mbarrier) through a per-warp ring of kStages tiles, so the
 // tile stream never waits for registers and runs ahead of the dependency waits.
 //
-// Scheduling.  Work is cut into tasks (forward: one row tile x up to kGroup column chunks; backward: one column chunk
+// Scheduling.  Work is cut into tasks (forward: a block of row tiles x column chunks, up to kGroup tiles; backward: one column chunk
 // x up to kGroup below row tiles), listed in elimination-tree level order over ALL subdomains.  Warps take tasks from
 // a ticket counter and synchronise point-to-point through per-supernode counters; a task only ever waits for tasks
 // with smaller ticket numbers, so the co-resident (cooperatively launched) grid cannot deadlock.
@@ -36,15 +36,15 @@ struct alignas(16) TriTask {
     const double *tiles;    // first tile of the task
     const int32_t *rowidx;  // fwd: 32 target offsets in WX (-1 = padding); bwd: 32 offsets per tile, consecutive tiles
     int32_t vec;            // fwd: offset in WX of y for the first column chunk; bwd: offset in WX of the 32 output columns
-    int32_t stride;         // doubles between consecutive tiles of the task
-    int16_t ntiles;
-    int16_t w;              // columns of every tile but the last
-    int16_t wlast;          // columns of the last tile (fwd: trailing chunk of the supernode)
-    int16_t signal_on;      // 1: add to signal_cnt on completion
+    int32_t stride;         // doubles between consecutive tiles of one group
+    int16_t ntiles;         // = groups x ncc
+    int16_t ncc;            // tiles per group (fwd: column chunks per row tile; bwd: all tiles form one group)
+    int16_t w;              // columns of every tile but the last of a group
+    int16_t wlast;          // columns of the last tile of a group (fwd: trailing chunk of the supernode)
     int32_t wait_cnt;       // counter index to wait on (-1: none)
     int32_t wait_need;
-    int32_t signal_cnt;
-    int32_t pad;
+    int32_t signal_cnt;     // counter to add 1 to on completion (-1: none)
+    int32_t gstride;        // doubles between consecutive groups (fwd: row tiles)
 };
 static_assert(sizeof(TriTask) == 48, "TriTask layout");
 

@@ -13,33 +13,38 @@ __global__ void __launch_bounds__(kTriWarps * 32, 1) trisolve_fwd_kernel(const T
     const int lane = w.lane;
     w.start();
     while (w.hasA) {
-        const int nt = w.A.ntiles;
-        const int tgt = __ldg(w.A.rowidx + lane);
+        const int ncc = w.A.ncc, ng = w.A.ntiles / ncc;
+        int tgt = __ldg(w.A.rowidx + lane);
         if (w.A.wait_cnt >= 0) wait_counter(cnt + w.A.wait_cnt, w.A.wait_need, lane);
         const double *yp = WX + w.A.vec + lane;
-        double ynext = (lane < (nt == 1 ? w.A.wlast : w.A.w)) ? __ldcg(yp) : 0.0;
-        double acc = 0.0;
-        for (int ti = 0; ti < nt; ++ti) {
-            const double yl = ynext;
-            if (ti + 1 < nt) {
-                const int wn = (ti + 2 == nt) ? w.A.wlast : w.A.w;
-                ynext = (lane < wn) ? __ldcg(yp + 32 * (ti + 1)) : 0.0;
-            }
-            const int wc = (ti == nt - 1) ? w.A.wlast : w.A.w;
-            const double *T = w.acquire_tile() + lane;
-            if (wc == 32) {
+        double ynext = (lane < (ncc == 1 ? w.A.wlast : w.A.w)) ? __ldcg(yp) : 0.0;
+        for (int g = 0; g < ng; ++g) {
+            double acc = 0.0;
+            for (int cc = 0; cc < ncc; ++cc) {
+                const double yl = ynext;
+                {   // y of the next tile (wraps to the first chunk for the next row tile)
+                    const int cn = (cc + 1 == ncc) ? 0 : cc + 1;
+                    const int wn = (cn == ncc - 1) ? w.A.wlast : w.A.w;
+                    ynext = (lane < wn) ? __ldcg(yp + 32 * cn) : 0.0;
+                }
+                const int wc = (cc == ncc - 1) ? w.A.wlast : w.A.w;
+                const double *T = w.acquire_tile() + lane;
+                if (wc == 32) {
 #pragma unroll
-                for (int j = 0; j < 32; ++j) acc = fma(T[j * 32], __shfl_sync(kFull, yl, j), acc);
-            } else {
+                    for (int j = 0; j < 32; ++j) acc = fma(T[j * 32], __shfl_sync(kFull, yl, j), acc);
+                } else {
 #pragma unroll 4
-                for (int j = 0; j < wc; ++j) acc = fma(T[j * 32], __shfl_sync(kFull, yl, j), acc);
+                    for (int j = 0; j < wc; ++j) acc = fma(T[j * 32], __shfl_sync(kFull, yl, j), acc);
+                }
+                w.release_tile();
             }
-            w.release_tile();
+            const int tnext = (g + 1 < ng) ? __ldg(w.A.rowidx + (g + 1) * 32 + lane) : -1;
+            if (tgt >= 0) atomicAdd(WX + tgt, acc);
+            tgt = tnext;
         }
-        if (tgt >= 0) atomicAdd(WX + tgt, acc);
         __threadfence();
         __syncwarp();
-        if (lane == 0 && w.A.signal_on) atomicAdd(cnt + w.A.signal_cnt, 1);
+        if (lane == 0 && w.A.signal_cnt >= 0) atomicAdd(cnt + w.A.signal_cnt, 1);
         w.advance();
     }
 }
@@ -93,7 +98,7 @@ __global__ void __launch_bounds__(kTriWarps * 32, 1) trisolve_bwd_kernel(const T
         if (lane < wc) atomicAdd(WX + w.A.vec + lane, acc[0]);
         __threadfence();
         __syncwarp();
-        if (lane == 0 && w.A.signal_on) atomicAdd(cnt + w.A.signal_cnt, 1);
+        if (lane == 0 && w.A.signal_cnt >= 0) atomicAdd(cnt + w.A.signal_cnt, 1);
         w.advance();
     }
 }

@@ -37,11 +37,12 @@ struct TriWarp {
     {
         if (lane == 0) {
             const unsigned slot = head % kStages;
-            const int wc = (ti == tk.ntiles - 1) ? tk.wlast : tk.w;
+            const int g = ti / tk.ncc, cc = ti - g * tk.ncc;
+            const int wc = (cc == tk.ncc - 1) ? tk.wlast : tk.w;
             const unsigned bytes = 256u * (unsigned)wc;
             fence_proxy_async();  // the slot was last read through the generic proxy
             mbar_expect_tx(bars + slot, bytes);
-            tma_load_1d(ring + (size_t)slot * kTileDoubles, tk.tiles + (size_t)ti * tk.stride, bytes, bars + slot);
+            tma_load_1d(ring + (size_t)slot * kTileDoubles, tk.tiles + (size_t)g * tk.gstride + (size_t)cc * tk.stride, bytes, bars + slot);
         }
         ++head;
     }
