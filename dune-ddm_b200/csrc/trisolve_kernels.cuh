@@ -4,6 +4,8 @@
 namespace ddm {
 
 // forward sweep: WX[rows] += panel(rows, chunks) * y(chunks)   (the panel holds D^{-1} rows and -Lt rows)
+// Per task the vector operand (<= kGroup chunks of y) and the row targets are staged once in shared memory, so the
+// tile loop touches shared memory only; the next ticket and descriptor are fetched while the tiles are consumed.
 __global__ void __launch_bounds__(kTriWarps * 32, 1) trisolve_fwd_kernel(const TriTask *__restrict__ tasks, int ntasks, double *WX,
                                                                           int *cnt, int *ticket)
 {
@@ -14,33 +16,46 @@ __global__ void __launch_bounds__(kTriWarps * 32, 1) trisolve_fwd_kernel(const T
     w.start();
     while (w.hasA) {
         const int ncc = w.A.ncc, ng = w.A.ntiles / ncc;
-        int tgt = __ldg(w.A.rowidx + lane);
+        w.prefetch_ticket();
+        int tg[kGroup];  // row targets: static data, fetched before the dependency wait
+#pragma unroll
+        for (int g = 0; g < kGroup; ++g) tg[g] = (g < ng) ? __ldg(w.A.rowidx + g * 32 + lane) : -1;
         if (w.A.wait_cnt >= 0) wait_counter(cnt + w.A.wait_cnt, w.A.wait_need, lane);
         const double *yp = WX + w.A.vec + lane;
-        double ynext = (lane < (ncc == 1 ? w.A.wlast : w.A.w)) ? __ldcg(yp) : 0.0;
+        double yv[kGroup];
+#pragma unroll
+        for (int cc = 0; cc < kGroup; ++cc) {
+            const int wn = (cc == ncc - 1) ? w.A.wlast : w.A.w;
+            yv[cc] = (cc < ncc && lane < wn) ? __ldcg(yp + 32 * cc) : 0.0;
+        }
+        w.prefetch_task();
+#pragma unroll
+        for (int g = 0; g < kGroup; ++g) {
+            w.idx[g * 32 + lane] = tg[g];
+            w.vals[g * 32 + lane] = yv[g];
+        }
+        __syncwarp();
         for (int g = 0; g < ng; ++g) {
-            double acc = 0.0;
+            double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
             for (int cc = 0; cc < ncc; ++cc) {
-                const double yl = ynext;
-                {   // y of the next tile (wraps to the first chunk for the next row tile)
-                    const int cn = (cc + 1 == ncc) ? 0 : cc + 1;
-                    const int wn = (cn == ncc - 1) ? w.A.wlast : w.A.w;
-                    ynext = (lane < wn) ? __ldcg(yp + 32 * cn) : 0.0;
-                }
                 const int wc = (cc == ncc - 1) ? w.A.wlast : w.A.w;
                 const double *T = w.acquire_tile() + lane;
+                const double *Y = w.vals + cc * 32;
                 if (wc == 32) {
 #pragma unroll
-                    for (int j = 0; j < 32; ++j) acc = fma(T[j * 32], __shfl_sync(kFull, yl, j), acc);
+                    for (int j = 0; j < 32; j += 4) {
+                        a0 = fma(T[j * 32], Y[j], a0);
+                        a1 = fma(T[(j + 1) * 32], Y[j + 1], a1);
+                        a2 = fma(T[(j + 2) * 32], Y[j + 2], a2);
+                        a3 = fma(T[(j + 3) * 32], Y[j + 3], a3);
+                    }
                 } else {
-#pragma unroll 4
-                    for (int j = 0; j < wc; ++j) acc = fma(T[j * 32], __shfl_sync(kFull, yl, j), acc);
+                    for (int j = 0; j < wc; ++j) a0 = fma(T[j * 32], Y[j], a0);
                 }
                 w.release_tile();
             }
-            const int tnext = (g + 1 < ng) ? __ldg(w.A.rowidx + (g + 1) * 32 + lane) : -1;
-            if (tgt >= 0) atomicAdd(WX + tgt, acc);
-            tgt = tnext;
+            const int tgt = w.idx[g * 32 + lane];
+            if (tgt >= 0) atomicAdd(WX + tgt, (a0 + a1) + (a2 + a3));
         }
         __threadfence();
         __syncwarp();
@@ -50,6 +65,8 @@ __global__ void __launch_bounds__(kTriWarps * 32, 1) trisolve_fwd_kernel(const T
 }
 
 // backward sweep: WX[cols] += panel(rows, cols)^T * x(rows)   (the panel holds -Lt)
+// The row lists (static) are fetched before the dependency wait, all x gathers of the task are issued together
+// after it and staged in shared memory.
 __global__ void __launch_bounds__(kTriWarps * 32, 1) trisolve_bwd_kernel(const TriTask *__restrict__ tasks, int ntasks, double *WX,
                                                                           int *cnt, int *ticket, int xoff)
 {
@@ -61,18 +78,23 @@ __global__ void __launch_bounds__(kTriWarps * 32, 1) trisolve_bwd_kernel(const T
     while (w.hasA) {
         const int nt = w.A.ntiles;
         const int wc = w.A.w;
-        int rnext = __ldg(w.A.rowidx + lane);
+        w.prefetch_ticket();
+        int rr[kGroup];
+#pragma unroll
+        for (int t = 0; t < kGroup; ++t) rr[t] = (t < nt) ? __ldg(w.A.rowidx + t * 32 + lane) : -1;
         if (w.A.wait_cnt >= 0) wait_counter(cnt + w.A.wait_cnt, w.A.wait_need, lane);
-        double xnext = (rnext >= 0) ? __ldcg(WX + xoff + rnext) : 0.0;  // row lists hold W offsets; x lives xoff further
+        double xv[kGroup];
+#pragma unroll
+        for (int t = 0; t < kGroup; ++t) xv[t] = (rr[t] >= 0) ? __ldcg(WX + xoff + rr[t]) : 0.0;  // row lists hold W offsets
+        w.prefetch_task();
+#pragma unroll
+        for (int t = 0; t < kGroup; ++t) w.vals[t * 32 + lane] = xv[t];
+        __syncwarp();
         double acc[32];
 #pragma unroll
         for (int j = 0; j < 32; ++j) acc[j] = 0.0;
         for (int ti = 0; ti < nt; ++ti) {
-            const double xr = xnext;
-            if (ti + 1 < nt) {
-                rnext = __ldg(w.A.rowidx + (ti + 1) * 32 + lane);
-                xnext = (rnext >= 0) ? __ldcg(WX + xoff + rnext) : 0.0;
-            }
+            const double xr = w.vals[ti * 32 + lane];
             const double *T = w.acquire_tile() + lane;
             if (wc == 32) {
 #pragma unroll

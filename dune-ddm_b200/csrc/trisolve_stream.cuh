@@ -11,9 +11,12 @@ struct TriWarp {
     int *ticket;
     double *ring;    // kStages tiles of this warp in shared memory
     uint64_t *bars;  // kStages mbarriers of this warp
+    double *vals;    // kGroup*32 doubles of this warp: the vector operand of the task (y chunks / gathered x)
+    int32_t *idx;    // kGroup*32 ints of this warp: row targets of the task
     int lane;
-    TriTask A, B;
+    TriTask A, B, C;
     bool hasA, hasB;
+    int tickC;       // lane 0: ticket requested ahead of time (-1: none pending)
     int issA, issB;
     unsigned head, tail;
 
@@ -54,8 +57,21 @@ struct TriWarp {
             else break;
         }
     }
+    // Requests the ticket after B (atomic in flight while the current task computes) ...
+    __device__ __forceinline__ void prefetch_ticket()
+    {
+        tickC = -1;
+        if (hasB && lane == 0) tickC = atomicAdd(ticket, 1);
+    }
+    // ... and later its descriptor (loads in flight until advance() needs them)
+    __device__ __forceinline__ void prefetch_task()
+    {
+        tickC = __shfl_sync(kFull, tickC, 0);
+        if (tickC >= 0 && tickC < ntasks) C = load_task(tasks + tickC);
+    }
     __device__ __forceinline__ void start()
     {
+        tickC = -1;
         head = tail = 0;
         issA = issB = 0;
         int t = take_ticket();
@@ -71,16 +87,14 @@ struct TriWarp {
     }
     __device__ __forceinline__ void advance()
     {
+        const bool hadB = hasB;
         A = B;
         hasA = hasB;
         issA = issB;
         issB = 0;
-        hasB = false;
-        if (hasA) {
-            const int t = take_ticket();
-            hasB = t < ntasks;
-            if (hasB) B = load_task(tasks + t);
-        }
+        hasB = hadB && tickC >= 0 && tickC < ntasks;
+        if (hasB) B = C;
+        tickC = -1;
         topup();
     }
     // waits for the next tile of A; returns its shared-memory address
@@ -98,7 +112,11 @@ struct TriWarp {
     }
 };
 
-constexpr size_t kTriSmemBytes = (size_t)kTriWarps * kStages * kTileDoubles * sizeof(double) + kTriWarps * kStages * sizeof(uint64_t);
+constexpr size_t kTriRingBytes = (size_t)kTriWarps * kStages * kTileDoubles * sizeof(double);
+constexpr size_t kTriBarBytes = (size_t)kTriWarps * kStages * sizeof(uint64_t);
+constexpr size_t kTriValBytes = (size_t)kTriWarps * kGroup * 32 * sizeof(double);
+constexpr size_t kTriIdxBytes = (size_t)kTriWarps * kGroup * 32 * sizeof(int32_t);
+constexpr size_t kTriSmemBytes = kTriRingBytes + kTriBarBytes + kTriValBytes + kTriIdxBytes;
 
 __device__ __forceinline__ void tri_setup(TriWarp &w, const TriTask *tasks, int ntasks, int *ticket, unsigned char *smem)
 {
@@ -108,7 +126,9 @@ __device__ __forceinline__ void tri_setup(TriWarp &w, const TriTask *tasks, int 
     w.ntasks = ntasks;
     w.ticket = ticket;
     w.ring = reinterpret_cast<double *>(smem) + (size_t)warp * kStages * kTileDoubles;
-    w.bars = reinterpret_cast<uint64_t *>(smem + (size_t)kTriWarps * kStages * kTileDoubles * sizeof(double)) + warp * kStages;
+    w.bars = reinterpret_cast<uint64_t *>(smem + kTriRingBytes) + warp * kStages;
+    w.vals = reinterpret_cast<double *>(smem + kTriRingBytes + kTriBarBytes) + warp * kGroup * 32;
+    w.idx = reinterpret_cast<int32_t *>(smem + kTriRingBytes + kTriBarBytes + kTriValBytes) + warp * kGroup * 32;
     if (w.lane == 0) {
         for (int s = 0; s < kStages; ++s) mbar_init(w.bars + s, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
