@@ -745,7 +745,7 @@ extern "C" int ddm_finalize(ddm_ctx *c)
     std::vector<int32_t> sn_base(ns + 1, 0);
     for (int32_t i = 0; i < ns; ++i) sn_base[i + 1] = sn_base[i] + (int32_t)c->fac[i].cw.size();
     c->nsn = sn_base[ns];
-    std::vector<int32_t> need(c->nsn, 0), nbwd(c->nsn, 0);
+    std::vector<int32_t> need(c->nsn, 0), nbwd(c->nsn, 0), haschild(c->nsn, 0);
     struct Key {
         int32_t level, sub, J, kind /* 0 below, 1 diag (fwd) */, a, b;  // fwd: row tile a, chunk group b; bwd: chunk a, row group b
     };
@@ -767,16 +767,27 @@ extern "C" int ddm_finalize(ddm_ctx *c)
             const int32_t cw = F.cw[J], nb = F.nb[J];
             const int32_t Rd = (cw + 31) / 32, Rb = (nb + 31) / 32, ncc = (cw + 31) / 32;
             const int32_t ngr = (Rb + kGroup - 1) / kGroup;
-            int32_t nf = 0;
+            int32_t nf = 0;  // forward tasks that touch below rows: the parent waits for these only
             if (ncc >= kGroup) {  // wide: one row tile x a group of chunks
                 const int32_t ngc = (ncc + kGroup - 1) / kGroup;
                 for (int32_t r = 0; r < Rd + Rb; ++r)
-                    for (int32_t g = 0; g < ngc; ++g, ++nf) fkeys.push_back({F.level[J], i, J, r < Rd ? 1 : 0, r, g});
+                    for (int32_t g = 0; g < ngc; ++g) {
+                        fkeys.push_back({F.level[J], i, J, r < Rd ? 1 : 0, r, g});
+                        if (r >= Rd) ++nf;
+                    }
             } else {  // narrow: several whole row tiles per task
                 const int32_t rpt = kGroup / ncc;
-                for (int32_t r = 0; r < Rd + Rb; r += rpt, ++nf) fkeys.push_back({F.level[J], i, J, 2, r, std::min(rpt, Rd + Rb - r)});
+                for (int32_t r = 0; r < Rd + Rb; r += rpt) {
+                    const int32_t nrt = std::min(rpt, Rd + Rb - r);
+                    const bool below = r + nrt > Rd;
+                    fkeys.push_back({F.level[J], i, J, below ? 2 : 3, r, nrt});
+                    if (below) ++nf;
+                }
             }
-            if (F.parent[J] >= 0) need[sn_base[i] + F.parent[J]] += nf;
+            if (F.parent[J] >= 0) {
+                need[sn_base[i] + F.parent[J]] += nf;
+                haschild[sn_base[i] + F.parent[J]] = 1;
+            }
             for (int32_t cc = 0; cc < ncc; ++cc)
                 for (int32_t g = 0; g < ngr; ++g) bkeys.push_back({F.level[J], i, J, 0, cc, g});
             nbwd[sn_base[i] + J] = ncc * ngr;
@@ -786,7 +797,11 @@ extern "C" int ddm_finalize(ddm_ctx *c)
         bytes_alg += 8.0 * F.nnz_lower;
     }
     // forward: ascending level, below-row tasks (they release the parent) before diagonal tasks of the same level
-    std::stable_sort(fkeys.begin(), fkeys.end(), [](const Key &a, const Key &b) { return a.level < b.level; });
+    // (kinds 1 and 3 are diagonal-only tasks: nobody waits for them, they fill the gaps)
+    std::stable_sort(fkeys.begin(), fkeys.end(), [](const Key &a, const Key &b) {
+        const int da = (a.kind & 1), db = (b.kind & 1);
+        return a.level != b.level ? a.level < b.level : da < db;
+    });
     std::stable_sort(bkeys.begin(), bkeys.end(), [](const Key &a, const Key &b) { return a.level > b.level; });
     std::vector<TriTask> fwd, bwd;
     fwd.reserve(fkeys.size());
@@ -796,7 +811,7 @@ extern "C" int ddm_finalize(ddm_ctx *c)
         const int32_t cw = F.cw[k.J], ncc = (cw + 31) / 32;
         TriTask t;
         int32_t c0 = 0, c1 = ncc, nrt = 1;
-        if (k.kind == 2) nrt = k.b;
+        if (k.kind >= 2) nrt = k.b;
         else {
             c0 = k.b * kGroup;
             c1 = std::min(ncc, c0 + kGroup);
@@ -812,7 +827,7 @@ extern "C" int ddm_finalize(ddm_ctx *c)
         t.wlast = (int16_t)std::min(32, cw - (c1 - 1) * 32);
         t.wait_cnt = need[sn_base[k.sub] + k.J] > 0 ? sn_base[k.sub] + k.J : -1;
         t.wait_need = need[sn_base[k.sub] + k.J];
-        t.signal_cnt = F.parent[k.J] >= 0 ? sn_base[k.sub] + F.parent[k.J] : -1;
+        t.signal_cnt = (F.parent[k.J] >= 0 && !(k.kind & 1)) ? sn_base[k.sub] + F.parent[k.J] : -1;
         fwd.push_back(t);
     }
     for (const Key &k : bkeys) {
@@ -831,7 +846,7 @@ extern "C" int ddm_finalize(ddm_ctx *c)
         t.w = t.wlast = (int16_t)std::min(32, cw - k.a * 32);
         t.wait_cnt = nbwd[par] > 0 ? c->nsn + par : -1;
         t.wait_need = nbwd[par];
-        t.signal_cnt = c->nsn + sn_base[k.sub] + k.J;
+        t.signal_cnt = haschild[sn_base[k.sub] + k.J] ? c->nsn + sn_base[k.sub] + k.J : -1;  // leaves: nobody waits
         bwd.push_back(t);
     }
     c->n_fwd = (int32_t)fwd.size();

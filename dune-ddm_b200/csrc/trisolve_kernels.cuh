@@ -57,9 +57,11 @@ __global__ void __launch_bounds__(kTriWarps * 32, 1) trisolve_fwd_kernel(const T
             const int tgt = w.idx[g * 32 + lane];
             if (tgt >= 0) atomicAdd(WX + tgt, (a0 + a1) + (a2 + a3));
         }
-        __threadfence();
-        __syncwarp();
-        if (lane == 0 && w.A.signal_cnt >= 0) atomicAdd(cnt + w.A.signal_cnt, 1);
+        if (w.A.signal_cnt >= 0) {  // somebody waits for this task: publish the accumulations, then count
+            __threadfence();
+            __syncwarp();
+            if (lane == 0) atomicAdd(cnt + w.A.signal_cnt, 1);
+        }
         w.advance();
     }
 }
@@ -118,9 +120,11 @@ __global__ void __launch_bounds__(kTriWarps * 32, 1) trisolve_bwd_kernel(const T
             }
         }
         if (lane < wc) atomicAdd(WX + w.A.vec + lane, acc[0]);
-        __threadfence();
-        __syncwarp();
-        if (lane == 0 && w.A.signal_cnt >= 0) atomicAdd(cnt + w.A.signal_cnt, 1);
+        if (w.A.signal_cnt >= 0) {  // somebody waits for this task: publish the accumulations, then count
+            __threadfence();
+            __syncwarp();
+            if (lane == 0) atomicAdd(cnt + w.A.signal_cnt, 1);
+        }
         w.advance();
     }
 }

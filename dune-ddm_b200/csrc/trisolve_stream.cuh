@@ -43,7 +43,7 @@ struct TriWarp {
             const int g = ti / tk.ncc, cc = ti - g * tk.ncc;
             const int wc = (cc == tk.ncc - 1) ? tk.wlast : tk.w;
             const unsigned bytes = 256u * (unsigned)wc;
-            fence_proxy_async();  // the slot was last read through the generic proxy
+            // no proxy fence: the slot's last generic-proxy reads completed before the __syncwarp in release_tile()
             mbar_expect_tx(bars + slot, bytes);
             tma_load_1d(ring + (size_t)slot * kTileDoubles, tk.tiles + (size_t)g * tk.gstride + (size_t)cc * tk.stride, bytes, bars + slot);
         }
