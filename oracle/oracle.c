@@ -236,3 +236,94 @@ int oracle_max_threads(void)
     return 1;
 #endif
 }
+
+/* Dune::RestartedGMResSolver::apply, /root/reference/extern/dune-istl/dune/istl/solvers.hh:923-1035 (left-preconditioned,
+ * modified Gram-Schmidt, Givens rotations :1072-1111, update :1039-1059).  The defect is the PRECONDITIONED residual norm
+ * |s[i+1]| (:948,1002); stopping rule as in oracle_pcg.  b is overwritten, x holds the solution.  Returns the iteration
+ * count; history gets maxit+1 entries. */
+static void gen_rot(double dx, double dy, double *cs, double *sn)
+{
+    const double eps = 1e-15, ndx = fabs(dx), ndy = fabs(dy);
+    const double nmax = ndx > ndy ? ndx : ndy, nmin = ndx > ndy ? ndy : ndx;
+    const double temp = nmin / nmax;
+    if (ndy < eps) { *cs = 1.0; *sn = 0.0; }
+    else if (ndx < eps) { *cs = 0.0; *sn = 1.0; }
+    else if (ndy > ndx) { *cs = 1.0 / sqrt(1.0 + temp * temp) * temp; *sn = 1.0 / sqrt(1.0 + temp * temp) * dx * dy / ndx / ndy; }
+    else { *cs = 1.0 / sqrt(1.0 + temp * temp); *sn = 1.0 / sqrt(1.0 + temp * temp) * (dy / dx); }
+}
+static void app_rot(double *dx, double *dy, double cs, double sn)
+{
+    const double t = cs * *dx + sn * *dy;
+    *dy = -sn * *dx + cs * *dy;
+    *dx = t;
+}
+
+int oracle_gmres(const oracle_setup *S, int restricted, int mode, int with_coarse, double *x, double *b, double reduction,
+                 int restart, int maxit, double *history, int *converged, int nthreads)
+{
+    const int64_t n = S->n;
+    const int m = restart;
+    double *s = calloc(m + 1, sizeof(double)), *sn = calloc(m, sizeof(double)), *cs = calloc(m, sizeof(double));
+    double *H = calloc((size_t)(m + 1) * m, sizeof(double)); /* H[k*m + i] */
+    double *b2 = malloc(sizeof(double) * n), *w = malloc(sizeof(double) * n), *t = malloc(sizeof(double) * n);
+    double **v = malloc(sizeof(double *) * (m + 1));
+    for (int k = 0; k <= m; ++k) v[k] = malloc(sizeof(double) * n);
+    memcpy(b2, b, sizeof(double) * n);
+    oracle_spmv(n, S->rowptr, S->col, S->val, x, t, nthreads);
+    for (int64_t q = 0; q < n; ++q) b[q] -= t[q];
+    oracle_twolevel_apply(S, restricted, mode, with_coarse, b, v[0], nthreads);
+    double norm = sqrt(oracle_dot(n, v[0], v[0]));
+    const double def0 = norm;
+    history[0] = norm;
+    *converged = (norm < def0 * reduction || norm < 1e-30);
+    int j = 1;
+    while (j <= maxit && !*converged) {
+        int i = 0;
+        const double inv = (norm == 0.0) ? 0.0 : 1.0 / norm;
+        for (int64_t q = 0; q < n; ++q) v[0][q] *= inv;
+        s[0] = norm;
+        for (i = 1; i < m + 1; ++i) s[i] = 0.0;
+        for (i = 0; i < m && j <= maxit && !*converged; ++i, ++j) {
+            oracle_spmv(n, S->rowptr, S->col, S->val, v[i], v[i + 1], nthreads);
+            oracle_twolevel_apply(S, restricted, mode, with_coarse, v[i + 1], w, nthreads);
+            for (int k = 0; k < i + 1; ++k) {
+                const double h = oracle_dot(n, v[k], w);
+                H[(size_t)k * m + i] = h;
+                for (int64_t q = 0; q < n; ++q) w[q] -= h * v[k][q];
+            }
+            const double hn = sqrt(oracle_dot(n, w, w));
+            H[(size_t)(i + 1) * m + i] = hn;
+            const double sc = (norm == 0.0) ? 0.0 : 1.0 / hn;
+            for (int64_t q = 0; q < n; ++q) v[i + 1][q] = w[q] * sc;
+            for (int k = 0; k < i; ++k) app_rot(&H[(size_t)k * m + i], &H[(size_t)(k + 1) * m + i], cs[k], sn[k]);
+            gen_rot(H[(size_t)i * m + i], H[(size_t)(i + 1) * m + i], &cs[i], &sn[i]);
+            app_rot(&H[(size_t)i * m + i], &H[(size_t)(i + 1) * m + i], cs[i], sn[i]);
+            app_rot(&s[i], &s[i + 1], cs[i], sn[i]);
+            norm = fabs(s[i + 1]);
+            history[j] = norm;
+            *converged = (norm < def0 * reduction || norm < 1e-30);
+        }
+        /* update(w, i, H, s, v) */
+        memset(w, 0, sizeof(double) * n);
+        double *y = malloc(sizeof(double) * (m + 1));
+        memcpy(y, s, sizeof(double) * (m + 1));
+        for (int a = i - 1; a >= 0; --a) {
+            double rhs = s[a];
+            for (int c = a + 1; c < i; ++c) rhs -= H[(size_t)a * m + c] * y[c];
+            y[a] = (rhs == 0.0) ? 0.0 : rhs / H[(size_t)a * m + a];
+            for (int64_t q = 0; q < n; ++q) w[q] += y[a] * v[a][q];
+        }
+        free(y);
+        for (int64_t q = 0; q < n; ++q) x[q] += w[q];
+        if (!*converged && j < maxit) {
+            memcpy(b, b2, sizeof(double) * n);
+            oracle_spmv(n, S->rowptr, S->col, S->val, x, t, nthreads);
+            for (int64_t q = 0; q < n; ++q) b[q] -= t[q];
+            oracle_twolevel_apply(S, restricted, mode, with_coarse, b, v[0], nthreads);
+            norm = sqrt(oracle_dot(n, v[0], v[0]));
+        }
+    }
+    for (int k = 0; k <= m; ++k) free(v[k]);
+    free(v); free(s); free(sn); free(cs); free(H); free(b2); free(w); free(t);
+    return j - 1;
+}

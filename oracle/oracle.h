@@ -42,6 +42,8 @@ void oracle_twolevel_apply(const oracle_setup *S, int restricted, int mode, int 
                            int nthreads);
 int oracle_pcg(const oracle_setup *S, int restricted, int mode, int with_coarse, double *x, double *b, double reduction,
                int maxit, double *history, int *converged, int nthreads);
+int oracle_gmres(const oracle_setup *S, int restricted, int mode, int with_coarse, double *x, double *b, double reduction,
+                 int restart, int maxit, double *history, int *converged, int nthreads);
 int oracle_max_threads(void);
 
 #ifdef __cplusplus

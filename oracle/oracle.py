@@ -34,6 +34,7 @@ def lib():
         _LIB = C.CDLL(path)
         _LIB.oracle_dot.restype = C.c_double
         _LIB.oracle_pcg.restype = C.c_int
+        _LIB.oracle_gmres.restype = C.c_int
         _LIB.oracle_max_threads.restype = C.c_int
     return _LIB
 
@@ -134,6 +135,17 @@ class Oracle:
         conv = C.c_int(0)
         it = lib().oracle_pcg(C.byref(self.S), C.c_int(int(restricted)), C.c_int(0 if mode == "additive" else 1), C.c_int(int(with_coarse)),
                               _p(x, C.c_double), _p(r, C.c_double), C.c_double(reduction), C.c_int(maxit), _p(hist, C.c_double), C.byref(conv), C.c_int(self.nthreads))
+        return x, it, bool(conv.value), hist[: it + 1]
+
+
+    def gmres(self, b, x0=None, reduction=1e-8, restart=30, maxit=1000, restricted=False, mode="additive", with_coarse=True):
+        x = np.zeros(self.P.n) if x0 is None else np.array(x0, dtype=np.float64)
+        r = np.array(b, dtype=np.float64)
+        hist = np.zeros(maxit + 1)
+        conv = C.c_int(0)
+        it = lib().oracle_gmres(C.byref(self.S), C.c_int(int(restricted)), C.c_int(0 if mode == "additive" else 1), C.c_int(int(with_coarse)),
+                                _p(x, C.c_double), _p(r, C.c_double), C.c_double(reduction), C.c_int(restart), C.c_int(maxit),
+                                _p(hist, C.c_double), C.byref(conv), C.c_int(self.nthreads))
         return x, it, bool(conv.value), hist[: it + 1]
 
 
