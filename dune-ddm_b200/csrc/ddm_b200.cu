@@ -105,6 +105,7 @@ struct SubFactor {
     // supernodes in elimination order
     std::vector<int32_t> col0, cw, nb, parent, level;
     std::vector<int64_t> tile_off;  // offset (doubles) of the supernode's first tile in `panel`
+    std::vector<int64_t> below_off; // offset of its first below-row tile (behind the diagonal block's tiles)
     std::vector<int64_t> row_off;   // offset of the supernode's row targets in `rowidx`
     double *panel = nullptr;        // device: tiles of [D^{-1}; -Lt] per supernode (trisolve.cuh)
     int32_t *rowidx = nullptr;      // device: absolute WX offsets, filled at finalize
@@ -420,6 +421,16 @@ extern "C" int ddm_upload_decomposition(ddm_ctx *c, int32_t nsub, const int64_t 
     return 0;
 }
 
+// Offset (doubles) of column chunk `c` inside the lower-triangular tile storage of a cw x cw symmetric block
+// (chunk-major: chunk c holds tiles r = c .. Rd-1, each 32 rows x w_c columns); c = number of chunks gives the total.
+static inline int64_t diag_tile_off(int32_t cw, int32_t c)
+{
+    const int64_t Rd = (cw + 31) / 32;
+    int64_t off = 1024 * ((int64_t)c * Rd - (int64_t)c * (c - 1) / 2);
+    if (c == Rd) off -= (int64_t)32 * (32 - (cw - (Rd - 1) * 32));  // the last chunk is narrower
+    return off;
+}
+
 extern "C" int ddm_upload_factor(ddm_ctx *c, int32_t sub, int32_t n, int32_t nsuper, const int32_t *super, const int64_t *pi,
                                  const int64_t *px, const int32_t *s, const double *x, const int32_t *perm)
 {
@@ -434,6 +445,7 @@ extern "C" int ddm_upload_factor(ddm_ctx *c, int32_t sub, int32_t n, int32_t nsu
     F.cw.resize(nsuper);
     F.nb.resize(nsuper);
     F.tile_off.resize(nsuper);
+    F.below_off.resize(nsuper);
     F.row_off.resize(nsuper);
     std::vector<int32_t> col2super(n, -1);
     std::vector<ConvTile> conv;
@@ -461,7 +473,10 @@ extern "C" int ddm_upload_factor(ddm_ctx *c, int32_t sub, int32_t n, int32_t nsu
         // row targets: diagonal rows are the supernode's own columns (in X), below rows its row structure (in W)
         for (int32_t r = 0; r < Rd * 32; ++r) F.rows_host.push_back(r < cw ? -2 - (f + r) : -1);  // encoded: -2-k = X position k
         for (int32_t r = 0; r < Rb * 32; ++r) F.rows_host.push_back(r < nb ? s[pi[J] + cw + r] : -1);
-        tile_doubles += (int64_t)(Rd + Rb) * 32 * cw;
+        // diagonal block: one full tile (cw <= 32) or the lower-triangular tiles of the symmetric inverse, chunk by chunk
+        const int64_t diag_doubles = cw <= 32 ? (int64_t)32 * cw : diag_tile_off(cw, Rd) ;
+        F.below_off[J] = tile_doubles + diag_doubles;
+        tile_doubles += diag_doubles + (int64_t)Rb * 32 * cw;
         nrows_tot += (int64_t)(Rd + Rb) * 32;
     }
     // aux layout: [small-supernode Linv | small-supernode Dinv | wide work space]
@@ -517,16 +532,18 @@ extern "C" int ddm_upload_factor(ddm_ctx *c, int32_t sub, int32_t n, int32_t nsu
             for (int32_t cc = 0; cc < ncc; ++cc) {
                 ConvTile ct;
                 ct.w = (int16_t)std::min(32, cw - cc * 32);
-                ct.dst = F.tile_off[J] + (int64_t)r * 32 * cw + (int64_t)cc * 1024;
                 ct.linv = 0;
-                if (r < Rd) {  // inverse diagonal block, full symmetric
+                if (r < Rd) {  // inverse diagonal block: lower-triangular tiles only (cw > 32), chunk-major
+                    if (cw > 32 && cc > r) continue;
                     ct.kind = 1;
                     ct.srcsel = 1;
                     ct.ld = cw;
                     ct.src = dinv_off[J] + (int64_t)cc * 32 * cw + (int64_t)r * 32;
                     ct.nrows = std::min(32, cw - r * 32);
+                    ct.dst = cw <= 32 ? F.tile_off[J] : F.tile_off[J] + diag_tile_off(cw, cc) + (int64_t)(r - cc) * 32 * ct.w;
                 } else {
                     const int32_t rb = r - Rd;
+                    ct.dst = F.below_off[J] + (int64_t)rb * 32 * cw + (int64_t)cc * 1024;
                     ct.srcsel = 0;
                     ct.ld = (int32_t)m;
                     ct.src = px[J] + (int64_t)cc * 32 * m + cw + (int64_t)rb * 32;
@@ -768,20 +785,24 @@ extern "C" int ddm_finalize(ddm_ctx *c)
             const int32_t Rd = (cw + 31) / 32, Rb = (nb + 31) / 32, ncc = (cw + 31) / 32;
             const int32_t ngr = (Rb + kGroup - 1) / kGroup;
             int32_t nf = 0;  // forward tasks that touch below rows: the parent waits for these only
-            if (ncc >= kGroup) {  // wide: one row tile x a group of chunks
-                const int32_t ngc = (ncc + kGroup - 1) / kGroup;
-                for (int32_t r = 0; r < Rd + Rb; ++r)
-                    for (int32_t g = 0; g < ngc; ++g) {
-                        fkeys.push_back({F.level[J], i, J, r < Rd ? 1 : 0, r, g});
-                        if (r >= Rd) ++nf;
-                    }
-            } else {  // narrow: several whole row tiles per task
-                const int32_t rpt = kGroup / ncc;
-                for (int32_t r = 0; r < Rd + Rb; r += rpt) {
-                    const int32_t nrt = std::min(rpt, Rd + Rb - r);
-                    const bool below = r + nrt > Rd;
+            if (cw <= 32) {  // one diagonal tile followed by the below row tiles: several whole row tiles per task
+                for (int32_t r = 0; r < 1 + Rb; r += kGroup) {
+                    const int32_t nrt = std::min((int32_t)kGroup, 1 + Rb - r);
+                    const bool below = r + nrt > 1;
                     fkeys.push_back({F.level[J], i, J, below ? 2 : 3, r, nrt});
                     if (below) ++nf;
+                }
+            } else {
+                // symmetric inverse diagonal block: column chunk c, up to kGroup-1 tiles r >= c per task (filler work)
+                for (int32_t cc = 0; cc < ncc; ++cc)
+                    for (int32_t r0 = cc; r0 < Rd; r0 += kGroup - 1) fkeys.push_back({F.level[J], i, J, 5, cc, r0});
+                if (ncc >= kGroup) {  // wide: one below row tile x a group of chunks
+                    const int32_t ngc = (ncc + kGroup - 1) / kGroup;
+                    for (int32_t r = 0; r < Rb; ++r)
+                        for (int32_t g = 0; g < ngc; ++g, ++nf) fkeys.push_back({F.level[J], i, J, 0, r, g});
+                } else {  // several whole below row tiles per task
+                    const int32_t rpt = kGroup / ncc;
+                    for (int32_t r = 0; r < Rb; r += rpt, ++nf) fkeys.push_back({F.level[J], i, J, 4, r, std::min(rpt, Rb - r)});
                 }
             }
             if (F.parent[J] >= 0) {
@@ -808,26 +829,48 @@ extern "C" int ddm_finalize(ddm_ctx *c)
     bwd.reserve(bkeys.size());
     for (const Key &k : fkeys) {
         const SubFactor &F = c->fac[k.sub];
-        const int32_t cw = F.cw[k.J], ncc = (cw + 31) / 32;
+        const int32_t cw = F.cw[k.J], ncc = (cw + 31) / 32, Rd = ncc;
+        const int32_t col_abs = (int32_t)(c->sub_ptr[k.sub] + F.col0[k.J]);
         TriTask t;
-        int32_t c0 = 0, c1 = ncc, nrt = 1;
-        if (k.kind >= 2) nrt = k.b;
-        else {
-            c0 = k.b * kGroup;
-            c1 = std::min(ncc, c0 + kGroup);
-        }
-        t.tiles = F.panel + F.tile_off[k.J] + (int64_t)k.a * 32 * cw + (int64_t)c0 * 1024;
-        t.rowidx = F.rowidx + F.row_off[k.J] + (int64_t)k.a * 32;
-        t.vec = (int32_t)(c->sub_ptr[k.sub] + F.col0[k.J] + c0 * 32);
         t.stride = 1024;
         t.gstride = 32 * cw;
-        t.ncc = (int16_t)(c1 - c0);
-        t.ntiles = (int16_t)(nrt * (c1 - c0));
         t.w = 32;
-        t.wlast = (int16_t)std::min(32, cw - (c1 - 1) * 32);
         t.wait_cnt = need[sn_base[k.sub] + k.J] > 0 ? sn_base[k.sub] + k.J : -1;
         t.wait_need = need[sn_base[k.sub] + k.J];
         t.signal_cnt = (F.parent[k.J] >= 0 && !(k.kind & 1)) ? sn_base[k.sub] + F.parent[k.J] : -1;
+        if (k.kind == 2 || k.kind == 3) {  // cw <= 32: row tiles a .. a+b of [diag; below]
+            t.tiles = F.panel + F.tile_off[k.J] + (int64_t)k.a * 32 * cw;
+            t.rowidx = F.rowidx + F.row_off[k.J] + (int64_t)k.a * 32;
+            t.vec = col_abs;
+            t.ncc = 1;
+            t.ntiles = (int16_t)k.b;
+            t.w = t.wlast = (int16_t)cw;
+        } else if (k.kind == 0) {  // below row tile a, chunk group b
+            const int32_t c0 = k.b * kGroup, c1 = std::min(ncc, c0 + kGroup);
+            t.tiles = F.panel + F.below_off[k.J] + (int64_t)k.a * 32 * cw + (int64_t)c0 * 1024;
+            t.rowidx = F.rowidx + F.row_off[k.J] + (int64_t)(Rd + k.a) * 32;
+            t.vec = col_abs + c0 * 32;
+            t.ncc = t.ntiles = (int16_t)(c1 - c0);
+            t.wlast = (int16_t)std::min(32, cw - (c1 - 1) * 32);
+        } else if (k.kind == 4) {  // below row tiles a .. a+b, all chunks
+            t.tiles = F.panel + F.below_off[k.J] + (int64_t)k.a * 32 * cw;
+            t.rowidx = F.rowidx + F.row_off[k.J] + (int64_t)(Rd + k.a) * 32;
+            t.vec = col_abs;
+            t.ncc = (int16_t)ncc;
+            t.ntiles = (int16_t)(k.b * ncc);
+            t.wlast = (int16_t)std::min(32, cw - (ncc - 1) * 32);
+        } else {  // kind 5: symmetric diagonal tiles (r, c), c = a, r = b .. b+nt
+            const int32_t cc = k.a, r0 = k.b, nt = std::min((int32_t)kGroup - 1, Rd - r0);
+            const int32_t wc = std::min(32, cw - cc * 32);
+            t.tiles = F.panel + F.tile_off[k.J] + diag_tile_off(cw, cc) + (int64_t)(r0 - cc) * 32 * wc;
+            t.rowidx = reinterpret_cast<const int32_t *>((intptr_t)(r0 - cc));  // sym tasks: first row tile relative to the chunk
+            t.vec = col_abs + cc * 32;
+            t.stride = 32 * wc;
+            t.gstride = cw - r0 * 32;  // valid rows counted from the first row tile
+            t.ncc = 0;                 // marks the task as symmetric
+            t.ntiles = (int16_t)nt;
+            t.w = t.wlast = (int16_t)wc;
+        }
         fwd.push_back(t);
     }
     for (const Key &k : bkeys) {
@@ -837,7 +880,7 @@ extern "C" int ddm_finalize(ddm_ctx *c)
         const int32_t r0 = k.b * kGroup, r1 = std::min(Rb, r0 + kGroup);
         const int32_t par = sn_base[k.sub] + F.parent[k.J];
         TriTask t;
-        t.tiles = F.panel + F.tile_off[k.J] + (int64_t)(Rd + r0) * 32 * cw + (int64_t)k.a * 1024;
+        t.tiles = F.panel + F.below_off[k.J] + (int64_t)r0 * 32 * cw + (int64_t)k.a * 1024;
         t.rowidx = F.rowidx + F.row_off[k.J] + (int64_t)(Rd + r0) * 32;
         t.vec = (int32_t)(P + c->sub_ptr[k.sub] + F.col0[k.J] + k.a * 32);
         t.stride = 32 * cw;
@@ -1026,7 +1069,8 @@ static int trisolve(ddm_ctx *c)
     int *cnt = c->cnt, *tick_f = c->cnt + 2 * c->nsn, *tick_b = tick_f + 1;
     {
         ScopedTimer tf(c, "Schwarz/local solve fwd");
-        void *args[] = {&c->fwd_tasks, &c->n_fwd, &c->W, &cnt, &tick_f};
+        int xoff = (int)c->P;
+        void *args[] = {&c->fwd_tasks, &c->n_fwd, &c->W, &cnt, &tick_f, &xoff};
         CU(cudaLaunchCooperativeKernel((void *)trisolve_fwd_kernel, dim3(c->tri_grid), dim3(kTriWarps * 32), args, kTriSmemBytes, c->s));
         c->launches++;
     }

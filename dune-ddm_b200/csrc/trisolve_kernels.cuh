@@ -7,7 +7,7 @@ namespace ddm {
 // Per task the vector operand (<= kGroup chunks of y) and the row targets are staged once in shared memory, so the
 // tile loop touches shared memory only; the next ticket and descriptor are fetched while the tiles are consumed.
 __global__ void __launch_bounds__(kTriWarps * 32, 1) trisolve_fwd_kernel(const TriTask *__restrict__ tasks, int ntasks, double *WX,
-                                                                          int *cnt, int *ticket)
+                                                                          int *cnt, int *ticket, int xoff)
 {
     extern __shared__ __align__(128) unsigned char tri_smem[];
     TriWarp w;
@@ -15,8 +15,68 @@ __global__ void __launch_bounds__(kTriWarps * 32, 1) trisolve_fwd_kernel(const T
     const int lane = w.lane;
     w.start();
     while (w.hasA) {
-        const int ncc = w.A.ncc, ng = w.A.ntiles / ncc;
+        const int ncc = w.A.ncc;
         w.prefetch_ticket();
+        if (ncc == 0) {
+            // Symmetric task on the inverse diagonal block: tiles (r, c) of its lower triangle, fixed chunk c.  Each tile
+            // is used twice: z_r += T y_c, and (off the diagonal) z_c += T^T y_r -- the upper triangle is never stored.
+            const int nt = w.A.ntiles, wc = w.A.w;
+            const int k0 = (int)(intptr_t)w.A.rowidx, nvalid = w.A.gstride;
+            if (w.A.wait_cnt >= 0) wait_counter(cnt + w.A.wait_cnt, w.A.wait_need, lane);
+            const double *yp = WX + w.A.vec + lane;
+            const double yc = (lane < wc) ? __ldcg(yp) : 0.0;
+            double yr[kGroup - 1];
+#pragma unroll
+            for (int t = 0; t < kGroup - 1; ++t) yr[t] = (t < nt && t * 32 + lane < nvalid) ? __ldcg(yp + (k0 + t) * 32) : 0.0;
+            w.prefetch_task();
+            w.vals[lane] = yc;
+#pragma unroll
+            for (int t = 0; t < kGroup - 1; ++t) w.vals[(1 + t) * 32 + lane] = yr[t];
+            __syncwarp();
+            double acc[32];
+#pragma unroll
+            for (int j = 0; j < 32; ++j) acc[j] = 0.0;
+            double *zr = WX + xoff + w.A.vec + lane;
+            for (int ti = 0; ti < nt; ++ti) {
+                const double xr = (k0 + ti == 0) ? 0.0 : w.vals[(1 + ti) * 32 + lane];  // diagonal tile: stored in full
+                const double *T = w.acquire_tile() + lane;
+                double a0 = 0.0, a1 = 0.0;
+                if (wc == 32) {
+#pragma unroll
+                    for (int j = 0; j < 32; j += 2) {
+                        const double t0 = T[j * 32], t1 = T[(j + 1) * 32];
+                        a0 = fma(t0, w.vals[j], a0);
+                        a1 = fma(t1, w.vals[j + 1], a1);
+                        acc[j] = fma(t0, xr, acc[j]);
+                        acc[j + 1] = fma(t1, xr, acc[j + 1]);
+                    }
+                } else {
+#pragma unroll
+                    for (int j = 0; j < 32; ++j)
+                        if (j < wc) {
+                            const double t0 = T[j * 32];
+                            a0 = fma(t0, w.vals[j], a0);
+                            acc[j] = fma(t0, xr, acc[j]);
+                        }
+                }
+                w.release_tile();
+                if (ti * 32 + lane < nvalid) atomicAdd(zr + (k0 + ti) * 32, a0 + a1);
+            }
+#pragma unroll
+            for (int half = 16; half >= 1; half >>= 1) {
+                const bool upper = (lane & half) != 0;
+#pragma unroll
+                for (int k = 0; k < half; ++k) {
+                    const double send = upper ? acc[k] : acc[k + half];
+                    const double keep = upper ? acc[k + half] : acc[k];
+                    acc[k] = keep + __shfl_xor_sync(kFull, send, half);
+                }
+            }
+            if (lane < wc) atomicAdd(zr, acc[0]);
+            w.advance();  // nobody waits for the diagonal block: no fence, no signal
+            continue;
+        }
+        const int ng = w.A.ntiles / ncc;
         int tg[kGroup];  // row targets: static data, fetched before the dependency wait
 #pragma unroll
         for (int g = 0; g < kGroup; ++g) tg[g] = (g < ng) ? __ldg(w.A.rowidx + g * 32 + lane) : -1;

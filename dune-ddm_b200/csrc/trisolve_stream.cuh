@@ -40,8 +40,8 @@ struct TriWarp {
     {
         if (lane == 0) {
             const unsigned slot = head % kStages;
-            const int g = ti / tk.ncc, cc = ti - g * tk.ncc;
-            const int wc = (cc == tk.ncc - 1) ? tk.wlast : tk.w;
+            const int g = tk.ncc > 0 ? ti / tk.ncc : 0, cc = ti - g * tk.ncc;  // ncc == 0: one group (symmetric task)
+            const int wc = (tk.ncc > 0 && cc == tk.ncc - 1) ? tk.wlast : tk.w;
             const unsigned bytes = 256u * (unsigned)wc;
             // no proxy fence: the slot's last generic-proxy reads completed before the __syncwarp in release_tile()
             mbar_expect_tx(bars + slot, bytes);
