@@ -27,8 +27,8 @@
 
 namespace ddm {
 
-constexpr int kStages = 3;          // tiles in flight per warp
-constexpr int kTriWarps = 8;        // warps per CTA (one CTA per SM): 8 * kStages * 8 KB = 192 KB of shared memory
+constexpr int kStages = 2;          // tiles in flight per warp
+constexpr int kTriWarps = 11;       // warps per CTA (one CTA per SM): 11 x (2 x 8 KB ring + 3 KB operands) = 209 KB of shared memory
 constexpr int kGroup = 8;           // tiles per task
 constexpr int kTileDoubles = 1024;  // 32 x 32
 
