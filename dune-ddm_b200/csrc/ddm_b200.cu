@@ -164,6 +164,9 @@ struct ddm_ctx {
     double *h_stage = nullptr;                  // pinned staging for *_host entry points (2*n_own)
     ddm_vec *hv[3] = {nullptr, nullptr, nullptr};
     ddm_vec *tmp[4] = {nullptr, nullptr, nullptr, nullptr};
+    std::vector<ddm_vec *> gm_v;  // GMRES basis v[0..m], w, b2 (allocated on first use)
+    double *gm_h = nullptr, *gm_hh = nullptr;  // one column of H: device, pinned host
+    int gm_cap = 0;
     // comm
     ncclComm_t comm = nullptr;
     int rank = 0, nranks = 1;
@@ -264,6 +267,9 @@ extern "C" int ddm_ctx_destroy(ddm_ctx *c)
     cudaStreamSynchronize(c->s);
     for (auto &v : c->hv) ddm_vec_destroy(v);
     for (auto &v : c->tmp) ddm_vec_destroy(v);
+    for (auto &v : c->gm_v) ddm_vec_destroy(v);
+    cudaFree(c->gm_h);
+    cudaFreeHost(c->gm_hh);
     for (auto &f : c->fac) free_factor(f);
     void *ptrs[] = {c->rowptr, c->col, c->val, c->A0, c->A0inv, c->d0, c->y0, c->r0, c->gidx, c->pouP, c->Zp, c->W,
                     c->zoff, c->d_sub_n, c->d_sub_k, c->d_koff, c->seg_ptr, c->segs, c->cpartial, c->dptr, c->dpos,
@@ -1222,6 +1228,138 @@ extern "C" int ddm_pcg_solve(ddm_ctx *c, ddm_vec *b, ddm_vec *x, double reductio
     return 0;
 }
 
+// ------------------------------------------------------------------------------------------------ GMRES
+// Dune::RestartedGMResSolver::apply (solvers.hh:923-1035): left-preconditioned, modified Gram-Schmidt, Givens rotations
+// (:1072-1111).  The Krylov basis and all vector work stay on the device; per Arnoldi step one column of H (i+2 scalars)
+// comes back to the host, where the (tiny) QR update runs exactly as in the reference.
+static void gen_rot(double dx, double dy, double &cs, double &sn)
+{
+    const double eps = 1e-15, ndx = std::fabs(dx), ndy = std::fabs(dy);
+    const double temp = std::min(ndx, ndy) / std::max(ndx, ndy);
+    if (ndy < eps) { cs = 1.0; sn = 0.0; }
+    else if (ndx < eps) { cs = 0.0; sn = 1.0; }
+    else if (ndy > ndx) { cs = 1.0 / std::sqrt(1.0 + temp * temp) * temp; sn = 1.0 / std::sqrt(1.0 + temp * temp) * dx * dy / ndx / ndy; }
+    else { cs = 1.0 / std::sqrt(1.0 + temp * temp); sn = 1.0 / std::sqrt(1.0 + temp * temp) * (dy / dx); }
+}
+static void app_rot(double &dx, double &dy, double cs, double sn)
+{
+    const double t = cs * dx + sn * dy;
+    dy = -sn * dx + cs * dy;
+    dx = t;
+}
+
+extern "C" int ddm_gmres_solve(ddm_ctx *c, ddm_vec *b, ddm_vec *x, double reduction, int32_t restart, int32_t maxit, int type,
+                               int mode, int with_coarse, ddm_result *res, double *history)
+{
+    CK(need_final(c));
+    if (restart < 1) return fail("GMRES restart must be >= 1");
+    const int m = restart;
+    const int64_t n = c->n_own;
+    // basis v[0..m], w, b2; column of H on the device (m+2 scalars) and pinned on the host
+    while ((int)c->gm_v.size() < m + 3) {
+        ddm_vec *v = nullptr;
+        CK(ddm_vec_create(c, &v));
+        c->gm_v.push_back(v);
+    }
+    if (c->gm_cap < m + 2) {
+        cudaFree(c->gm_h);
+        cudaFreeHost(c->gm_hh);
+        CU(cudaMalloc((void **)&c->gm_h, sizeof(double) * (m + 2)));
+        CU(cudaMallocHost((void **)&c->gm_hh, sizeof(double) * (m + 2)));
+        c->gm_cap = m + 2;
+    }
+    ddm_vec **v = c->gm_v.data(), *w = c->gm_v[m + 1], *b2 = c->gm_v[m + 2];
+    std::vector<double> s(m + 1), sn(m), cs(m), H((size_t)(m + 1) * m, 0.0);
+    cudaEvent_t e0, e1;
+    CU(cudaEventCreate(&e0));
+    CU(cudaEventCreate(&e1));
+    CU(cudaEventRecord(e0, c->s));
+    auto dot_to = [&](const double *vk, const double *vprev, const double *hprev, int slot) -> int {
+        LAUNCH(c, mgs_kernel, c->nred, 256, n, hprev, vprev, vk, w->d, c->partial);
+        LAUNCH(c, reduce_final_kernel, 1, 256, c->nred, c->partial, c->gm_h + slot);
+        if (c->nranks > 1) NC(g_nccl.AllReduce(c->gm_h + slot, c->gm_h + slot, 1, ncclDouble, ncclSum, c->comm, c->s));
+        return 0;
+    };
+    auto norm_of = [&](ddm_vec *u, double *out) -> int {
+        CK(dot_dev(c, u->d, u->d, 2));
+        double t;
+        CK(fetch_scalar(c, 2, &t));
+        *out = std::sqrt(t);
+        return 0;
+    };
+    auto conv_of = [&](double nrm, double def0) { return nrm < def0 * reduction || nrm < 1e-30; };
+
+    CK(ddm_vec_copy(b2, b));
+    CK(spmv(c, x->d, b->d, -1.0, 1));  // b -= A x
+    CK(ddm_twolevel_apply(c, type, mode, with_coarse, b, v[0]));
+    double norm = 0.0;
+    CK(norm_of(v[0], &norm));
+    const double def0 = norm;
+    if (history) history[0] = norm;
+    if (!std::isfinite(norm)) return fail("GMRes: defect is infinite or NaN");
+    bool conv = conv_of(norm, def0);
+    int j = 1;
+    while (j <= maxit && !conv) {
+        int i = 0;
+        CK(ddm_vec_scale(v[0], norm == 0.0 ? 0.0 : 1.0 / norm));
+        s[0] = norm;
+        for (i = 1; i < m + 1; ++i) s[i] = 0.0;
+        for (i = 0; i < m && j <= maxit && !conv; ++i, ++j) {
+            CK(spmv(c, v[i]->d, v[i + 1]->d, 1.0, 0));
+            CK(ddm_twolevel_apply(c, type, mode, with_coarse, v[i + 1], w));
+            for (int k = 0; k <= i; ++k)  // H[k][i] = v_k . w after w -= H[k-1][i] v_{k-1}
+                CK(dot_to(v[k]->d, k ? v[k - 1]->d : nullptr, k ? c->gm_h + k - 1 : nullptr, k));
+            CK(dot_to(nullptr, v[i]->d, c->gm_h + i, i + 1));  // w -= H[i][i] v_i ; |w|^2
+            LAUNCH(c, normalize_kernel, stream_grid(c, n), 256, n, c->gm_h + i + 1, norm == 0.0 ? 1 : 0, w->d, v[i + 1]->d);
+            CU(cudaMemcpyAsync(c->gm_hh, c->gm_h, sizeof(double) * (i + 2), cudaMemcpyDeviceToHost, c->s));
+            CU(cudaStreamSynchronize(c->s));
+            for (int k = 0; k <= i; ++k) H[(size_t)k * m + i] = c->gm_hh[k];
+            const double hn = std::sqrt(c->gm_hh[i + 1]);
+            H[(size_t)(i + 1) * m + i] = hn;
+            if (!std::isfinite(hn)) return fail("GMRes: defect is infinite or NaN at iteration %d", j);
+            if (std::fabs(hn) < 1e-80) return fail("breakdown in GMRes - |w| == 0.0 after %d iterations", j);  // solvers.hh:983
+            for (int k = 0; k < i; ++k) app_rot(H[(size_t)k * m + i], H[(size_t)(k + 1) * m + i], cs[k], sn[k]);
+            gen_rot(H[(size_t)i * m + i], H[(size_t)(i + 1) * m + i], cs[i], sn[i]);
+            app_rot(H[(size_t)i * m + i], H[(size_t)(i + 1) * m + i], cs[i], sn[i]);
+            app_rot(s[i], s[i + 1], cs[i], sn[i]);
+            norm = std::fabs(s[i + 1]);
+            if (history) history[j] = norm;
+            conv = conv_of(norm, def0);
+        }
+        // update(w, i, H, s, v) and x += w (solvers.hh:1009-1012, 1039-1059)
+        CK(ddm_vec_fill(w, 0.0));
+        std::vector<double> y(s);
+        for (int a = i - 1; a >= 0; --a) {
+            double rhs = s[a];
+            for (int q = a + 1; q < i; ++q) rhs -= H[(size_t)a * m + q] * y[q];
+            y[a] = rhs == 0.0 ? 0.0 : rhs / H[(size_t)a * m + a];
+            CK(ddm_vec_axpy(w, y[a], v[a]));
+        }
+        CK(ddm_vec_add(x, w));
+        if (!conv && j < maxit) {  // restart
+            CK(ddm_vec_copy(b, b2));
+            CK(spmv(c, x->d, b->d, -1.0, 1));
+            CK(ddm_twolevel_apply(c, type, mode, with_coarse, b, v[0]));
+            CK(norm_of(v[0], &norm));
+        }
+    }
+    CU(cudaEventRecord(e1, c->s));
+    CU(cudaEventSynchronize(e1));
+    float ms = 0;
+    CU(cudaEventElapsedTime(&ms, e0, e1));
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    if (res) {
+        res->iterations = j - 1;
+        res->converged = conv ? 1 : 0;
+        res->reduction = def0 > 0 ? norm / def0 : 0.0;
+        res->conv_rate = j > 1 ? std::pow(res->reduction, 1.0 / (j - 1)) : 0.0;
+        res->elapsed = ms * 1e-3;
+        res->def0 = def0;
+    }
+    return 0;
+}
+
 // ------------------------------------------------------------------------------------------------ host-pointer forms
 static int stage_in(ddm_ctx *c, ddm_vec *v, const double *h, int slot)
 {
@@ -1274,6 +1412,17 @@ extern "C" int ddm_pcg_solve_host(ddm_ctx *c, double *b, double *x, double reduc
     CK(stage_in(c, c->hv[0], b, 0));
     CK(stage_in(c, c->hv[1], x, 1));
     CK(ddm_pcg_solve(c, c->hv[0], c->hv[1], reduction, maxit, type, mode, with_coarse, res, history));
+    CK(stage_out(c, c->hv[0], b, 0));
+    return stage_out(c, c->hv[1], x, 1);
+}
+
+extern "C" int ddm_gmres_solve_host(ddm_ctx *c, double *b, double *x, double reduction, int32_t restart, int32_t maxit, int type,
+                                    int mode, int with_coarse, ddm_result *res, double *history)
+{
+    CK(need_final(c));
+    CK(stage_in(c, c->hv[0], b, 0));
+    CK(stage_in(c, c->hv[1], x, 1));
+    CK(ddm_gmres_solve(c, c->hv[0], c->hv[1], reduction, restart, maxit, type, mode, with_coarse, res, history));
     CK(stage_out(c, c->hv[0], b, 0));
     return stage_out(c, c->hv[1], x, 1);
 }

@@ -131,6 +131,36 @@ __global__ void __launch_bounds__(256) cg_update_kernel(int64_t n, const double 
     if (threadIdx.x == 0) partial[blockIdx.x] = t;
 }
 
+// modified Gram-Schmidt step of RestartedGMResSolver (solvers.hh:975-981), two passes fused into one:
+//   w -= h_prev * v_prev  (the axpy of the previous k, scalar on the device), then the partial of  v_k . w
+// (v_k == nullptr: partial of |w|^2, the norm that closes the Arnoldi step, :982).
+__global__ void __launch_bounds__(256) mgs_kernel(int64_t n, const double *__restrict__ hprev, const double *__restrict__ vprev,
+                                                  const double *__restrict__ vk, double *__restrict__ w,
+                                                  double *__restrict__ partial)
+{
+    __shared__ double sm[8];
+    const double h = vprev ? *hprev : 0.0;
+    double acc = 0.0;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        double wi = w[i];
+        if (vprev) {
+            wi = fma(-h, vprev[i], wi);
+            w[i] = wi;
+        }
+        acc = fma(vk ? vk[i] : wi, wi, acc);
+    }
+    const double t = block_sum_256(acc, sm);
+    if (threadIdx.x == 0) partial[blockIdx.x] = t;
+}
+// dst = src * (1 / sqrt(nrm2)) (v[i+1] = w; v[i+1] *= 1/H[i+1][i], solvers.hh:988-991); zero != 0 gives dst = 0
+__global__ void normalize_kernel(int64_t n, const double *__restrict__ nrm2, int zero, const double *__restrict__ src,
+                                 double *__restrict__ dst)
+{
+    const double a = zero ? 0.0 : 1.0 / sqrt(*nrm2);
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+        dst[i] = src[i] * a;
+}
+
 // ------------------------------------------------------------------------------------------------
 // K2 + K5  restriction of the defect to all hosted subdomains, fused with the coarse restriction.
 // schwarz.hh:121-125 / galerkin_preconditioner.hh:159-167: W[p] = d[gidx[p]] (pivot order), and for the

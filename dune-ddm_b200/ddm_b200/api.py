@@ -375,3 +375,118 @@ class CGSolver:
         check(s.ctx.lib.ddm_pcg_solve_host(s.ctx.h, _p(b, C.c_double), _p(x, C.c_double), C.c_double(self.reduction), C.c_int32(self.maxit),
                                            C.c_int(s.type), C.c_int(self.prec.mode), C.c_int(int(len(self.prec.precs) > 1)), C.byref(res), _p(hist, C.c_double)))
         return x, InverseOperatorResult(res.iterations, bool(res.converged), res.reduction, res.conv_rate, res.elapsed, hist[: res.iterations + 1])
+
+
+class RestartedGMResSolver:
+    """Dune::RestartedGMResSolver (solvers.hh:923-1035) over the same three interfaces.
+
+    apply() is the literal drop-in loop (every dot and norm returns to the host where the reference reads it);
+    solve_device() / solve_host() run ddm_gmres_solve: basis and vector work on the GPU, one column of H per step
+    comes back for the Givens update.
+    """
+
+    def __init__(self, op, sp, prec, reduction=1e-8, restart=30, maxit=100, verbose=0):
+        self.op, self.sp, self.prec = op, sp, prec
+        self.reduction, self.restart, self.maxit, self.verbose = reduction, restart, maxit, verbose
+
+    @staticmethod
+    def _gen_rot(dx, dy):
+        eps, ndx, ndy = 1e-15, abs(dx), abs(dy)
+        if ndy < eps:
+            return 1.0, 0.0
+        if ndx < eps:
+            return 0.0, 1.0
+        temp = min(ndx, ndy) / max(ndx, ndy)
+        if ndy > ndx:
+            return 1.0 / np.sqrt(1.0 + temp * temp) * temp, 1.0 / np.sqrt(1.0 + temp * temp) * dx * dy / ndx / ndy
+        return 1.0 / np.sqrt(1.0 + temp * temp), 1.0 / np.sqrt(1.0 + temp * temp) * (dy / dx)
+
+    def apply(self, x, b):
+        ctx, m = x.ctx, self.restart
+        hist = []
+        s, sn, cs = np.zeros(m + 1), np.zeros(m), np.zeros(m)
+        H = np.zeros((m + 1, m))
+        b2, w = ctx.vector().assign(b), ctx.vector()
+        v = [ctx.vector() for _ in range(m + 1)]
+        self.prec.pre(x, b)
+        self.op.applyscaleadd(-1.0, x, b)
+        v[0].fill(0.0)
+        self.prec.apply(v[0], b)
+        norm = self.sp.norm(v[0])
+        def0 = norm
+        hist.append(norm)
+        if not np.isfinite(norm):
+            raise DDMError("GMRes: defect is infinite or NaN")
+
+        def conv(val):
+            return val < def0 * self.reduction or val < 1e-30
+
+        done = conv(norm)
+        j = 1
+        while j <= self.maxit and not done:
+            v[0] *= 0.0 if norm == 0.0 else 1.0 / norm
+            s[:] = 0.0
+            s[0] = norm
+            i = 0
+            while i < m and j <= self.maxit and not done:
+                w.fill(0.0)
+                v[i + 1].fill(0.0)
+                self.op.apply(v[i], v[i + 1])
+                self.prec.apply(w, v[i + 1])
+                for k in range(i + 1):
+                    H[k, i] = self.sp.dot(v[k], w)
+                    w.axpy(-H[k, i], v[k])
+                H[i + 1, i] = self.sp.norm(w)
+                if abs(H[i + 1, i]) < 1e-80:
+                    raise DDMError(f"breakdown in GMRes - |w| == 0.0 after {j} iterations")  # SolverAbort, solvers.hh:983
+                v[i + 1].assign(w)
+                v[i + 1] *= 0.0 if norm == 0.0 else 1.0 / H[i + 1, i]
+                for k in range(i):
+                    H[k, i], H[k + 1, i] = cs[k] * H[k, i] + sn[k] * H[k + 1, i], -sn[k] * H[k, i] + cs[k] * H[k + 1, i]
+                cs[i], sn[i] = self._gen_rot(H[i, i], H[i + 1, i])
+                H[i, i], H[i + 1, i] = cs[i] * H[i, i] + sn[i] * H[i + 1, i], -sn[i] * H[i, i] + cs[i] * H[i + 1, i]
+                s[i], s[i + 1] = cs[i] * s[i] + sn[i] * s[i + 1], -sn[i] * s[i] + cs[i] * s[i + 1]
+                norm = abs(s[i + 1])
+                hist.append(norm)
+                if not np.isfinite(norm):
+                    raise DDMError("GMRes: defect is infinite or NaN")
+                done = conv(norm)
+                i += 1
+                j += 1
+            w.fill(0.0)
+            y = s.copy()
+            for a in range(i - 1, -1, -1):
+                rhs = s[a] - H[a, a + 1 : i] @ y[a + 1 : i]
+                y[a] = 0.0 if rhs == 0.0 else rhs / H[a, a]
+                w.axpy(y[a], v[a])
+            x += w
+            if not done and j < self.maxit:
+                b.assign(b2)
+                self.op.applyscaleadd(-1.0, x, b)
+                v[0].fill(0.0)
+                self.prec.apply(v[0], b)
+                norm = self.sp.norm(v[0])
+        self.prec.post(x)
+        red = norm / def0 if def0 > 0 else 0.0
+        return InverseOperatorResult(j - 1, done, red, red ** (1.0 / (j - 1)) if j > 1 else 0.0, 0.0, np.array(hist))
+
+    def _args(self):
+        s = self.prec.precs[0]
+        return s, (C.c_double(self.reduction), C.c_int32(self.restart), C.c_int32(self.maxit), C.c_int(s.type), C.c_int(self.prec.mode),
+                   C.c_int(int(len(self.prec.precs) > 1)))
+
+    def solve_device(self, x, b):
+        s, args = self._args()
+        res = Result()
+        hist = np.zeros(self.maxit + 1)
+        check(s.ctx.lib.ddm_gmres_solve(s.ctx.h, b.h, x.h, *args, C.byref(res), _p(hist, C.c_double)))
+        return InverseOperatorResult(res.iterations, bool(res.converged), res.reduction, res.conv_rate, res.elapsed, hist[: res.iterations + 1])
+
+    def solve_host(self, b_host, x_host=None):
+        s, args = self._args()
+        b = np.array(b_host, dtype=np.float64)
+        x = np.zeros_like(b) if x_host is None else np.array(x_host, dtype=np.float64)
+        res = Result()
+        hist = np.zeros(self.maxit + 1)
+        check(s.ctx.lib.ddm_gmres_solve_host(s.ctx.h, _p(b, C.c_double), _p(x, C.c_double), *args, C.byref(res), _p(hist, C.c_double)))
+        return x, InverseOperatorResult(res.iterations, bool(res.converged), res.reduction, res.conv_rate, res.elapsed, hist[: res.iterations + 1])

@@ -139,6 +139,12 @@ int ddm_twolevel_apply(ddm_ctx *ctx, int schwarz_type, int combine_mode, int wit
 int ddm_pcg_solve(ddm_ctx *ctx, ddm_vec *b, ddm_vec *x, double reduction, int32_t maxit, int schwarz_type,
                   int combine_mode, int with_coarse, ddm_result *res, double *history);
 
+/* Dune::RestartedGMResSolver::apply (extern/dune-istl/dune/istl/solvers.hh:923-1035): left-preconditioned GMRES(restart),
+ * modified Gram-Schmidt, Givens rotations (:1072-1111); the defect is the preconditioned residual norm |s[i+1]|.
+ * A breakdown (|w| < 1e-80, :983) returns a non-zero status (the reference throws SolverAbort). */
+int ddm_gmres_solve(ddm_ctx *ctx, ddm_vec *b, ddm_vec *x, double reduction, int32_t restart, int32_t maxit, int schwarz_type,
+                    int combine_mode, int with_coarse, ddm_result *res, double *history);
+
 /* ---- host-pointer forms (stage through pinned memory; owned entries only) ---------------
  * These are what an adaptor with X = Dune::BlockVector<FieldVector<double,1>> calls. */
 int ddm_op_apply_host(ddm_ctx *ctx, const double *x, double *y);
@@ -148,6 +154,9 @@ int ddm_twolevel_apply_host(ddm_ctx *ctx, int schwarz_type, int combine_mode, in
                             double *x);
 int ddm_pcg_solve_host(ddm_ctx *ctx, double *b, double *x, double reduction, int32_t maxit, int schwarz_type,
                        int combine_mode, int with_coarse, ddm_result *res, double *history);
+
+int ddm_gmres_solve_host(ddm_ctx *ctx, double *b, double *x, double reduction, int32_t restart, int32_t maxit,
+                         int schwarz_type, int combine_mode, int with_coarse, ddm_result *res, double *history);
 
 /* ---- introspection ---------------------------------------------------------------------- */
 /* Algorithmic bytes per call of each kernel family and launch counters, for roofline reports.

@@ -205,3 +205,34 @@ def test_stats_and_timers(case):
     ms, calls = ctx.timer("Schwarz/local solve")  # the reference's Logger event names (schwarz.hh:178-182)
     assert calls == 3 and ms > 0
     ctx.timers(False)
+
+
+@pytest.mark.parametrize("typ,mode", [("restricted", "multiplicative"), ("standard", "additive")])
+def test_gmres_dropin_and_device_loops(case, typ, mode):
+    """RestartedGMResSolver (solvers.hh:923-1035): the literal loop over the three interfaces and ddm_gmres_solve against the
+    oracle's restatement (which tests/test_ref_krylov.py pins to the real Dune solver).  Restart 8 forces restarts."""
+    from ddm_b200 import api
+
+    P, ctx, O, _, _ = case
+    op, sp = api.NonOverlappingOperator(ctx), api.NonOverlappingScalarProduct(ctx)
+    C = api.CombinedPreconditioner(mode)
+    C.set_op(op)
+    C.add(api.SchwarzPreconditioner(ctx, typ))
+    C.add(api.GalerkinPreconditioner(ctx))
+    gm = api.RestartedGMResSolver(op, sp, C, reduction=1e-8, restart=8, maxit=200)
+    xo, ito, convo, histo = O.gmres(P.b, reduction=1e-8, restart=8, maxit=200, restricted=typ == "restricted", mode=mode)
+    assert convo
+    x, b = ctx.vector(np.zeros(P.n)), ctx.vector(P.b)
+    r1 = gm.apply(x, b)
+    assert r1.converged and abs(r1.iterations - ito) <= 1
+    assert np.allclose(r1.history[:5], histo[:5], rtol=1e-8)
+    x2, b2 = ctx.vector(np.zeros(P.n)), ctx.vector(P.b)
+    r2 = gm.solve_device(x2, b2)
+    assert r2.converged and abs(r2.iterations - ito) <= 1
+    assert np.allclose(r2.history[:5], histo[:5], rtol=1e-8)
+    xh, r3 = gm.solve_host(P.b)
+    assert r3.converged and abs(r3.iterations - ito) <= 1
+    scale = np.linalg.norm(xo)
+    for got in (x.download(), x2.download(), xh):
+        assert np.linalg.norm(got - xo) <= 1e-6 * scale  # both stop on the preconditioned defect; cond(M A) small
+        assert np.linalg.norm(P.b - P.A @ got) <= 1e-6 * np.linalg.norm(P.b)
