@@ -60,18 +60,25 @@ def workload_name(a, world):
             f"{a.nsub * world} subdomains (RCB), overlap {a.overlap}, {a.coarse} coarse space nev {a.nev}, additive, CG 1e-8")
 
 
-def build_problem(a, world):
+def build_problem(a, world, rank=None, gather=None):
+    """rank/gather given: this process builds only its own subdomains' factors and bases (one process per GPU)."""
     from ddm_b200.setup import fem, mesh, pack, problem
 
-    if a.pack and os.path.exists(a.pack):
+    if a.pack and os.path.exists(a.pack) and gather is None:
         return pack.load_products(a.pack)
-    P = _build_problem(a, world, fem, mesh, problem)
-    if a.pack:
+    kw = {}
+    if gather is not None:
+        from ddm_b200.partition import sub_ranges
+
+        s0, s1 = sub_ranges(a.nsub * world, world)[rank]
+        kw = dict(only=range(s0, s1), gather=gather, workers=max(1, (os.cpu_count() or 1) // world))
+    P = _build_problem(a, world, fem, mesh, problem, **kw)
+    if a.pack and gather is None:
         pack.save_products(a.pack, P)
     return P
 
 
-def _build_problem(a, world, fem, mesh, problem):
+def _build_problem(a, world, fem, mesh, problem, **kw):
     g = gpu_grid(world)
     shape = tuple(a.ncell * k for k in g)
     coords, cells = mesh.structured_simplices(shape, lengths=tuple(float(k) for k in g))
@@ -80,7 +87,7 @@ def _build_problem(a, world, fem, mesh, problem):
         return fem.kappa_islands(cent - np.floor(cent))
 
     return problem.poisson_simplex(coords, cells, a.nsub * world, kappa_fn=kappa, xmax=float(g[0]), overlap=a.overlap,
-                                   coarse=a.coarse, nev=a.nev, meta=dict(mesh=f"kuhn-{shape}"))
+                                   coarse=a.coarse, nev=a.nev, meta=dict(mesh=f"kuhn-{shape}"), **kw)
 
 
 class ClockSampler:
@@ -193,15 +200,24 @@ def run_b200(a):
     import torch.distributed as dist
 
     uid = None
+    gather = None
     if world > 1:
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        # torch.distributed is host-side plumbing only (setup exchange, barrier, max over ranks): gloo.  The data path's
+        # collectives (halo exchange, coarse all-reduce, Krylov scalars) are NCCL calls inside libddm_b200.so.
+        dist.init_process_group("gloo")
+
+        def gather(obj):
+            out = [None] * world
+            dist.all_gather_object(out, obj)
+            return out
+
     from ddm_b200 import api, lib
 
     t0 = time.perf_counter()
-    P = build_problem(a, world)
+    P = build_problem(a, world, rank, gather)
     if rank == 0:
         print(f"[bench] host setup {time.perf_counter() - t0:.1f} s: n={P.n} nsub={P.nsub} N0={P.A0.shape[0]} "
-              f"nnz(L)={sum(F.nnz_lower() for F in P.factors) / 1e6:.1f} M", file=sys.stderr, flush=True)
+              f"nnz(L) on rank 0 = {sum(F.nnz_lower() for F in P.factors if F is not None) / 1e6:.1f} M", file=sys.stderr, flush=True)
     t0 = time.perf_counter()
     if world > 1:
         import ctypes as C
@@ -209,9 +225,9 @@ def run_b200(a):
         buf = (C.c_uint8 * 128)()
         if rank == 0:
             api.check(lib.load().ddm_comm_unique_id(buf))
-        t = torch.tensor(list(buf), dtype=torch.uint8, device="cuda")
+        t = torch.tensor(list(buf), dtype=torch.uint8)
         dist.broadcast(t, 0)
-        uid = t.cpu().tolist()
+        uid = t.tolist()
     ctx = api.Context.from_products(P, device=local, rank=rank, world=world, unique_id=uid)
     if rank == 0:
         print(f"[bench] upload + device schedules {time.perf_counter() - t0:.1f} s", file=sys.stderr, flush=True)
@@ -266,7 +282,7 @@ def run_b200(a):
     barrier()
     t_e2e = time.perf_counter() - t0
     # ---- reduce over ranks
-    vals = torch.tensor([dev_ms, t_wall, t_e2e], dtype=torch.float64, device="cuda")
+    vals = torch.tensor([dev_ms, t_wall, t_e2e], dtype=torch.float64)
     if world > 1:
         dist.all_reduce(vals, op=dist.ReduceOp.MAX)
     dev_ms, t_wall, t_e2e = vals.tolist()
@@ -292,6 +308,12 @@ def run_b200(a):
     dom = max(kern, key=lambda k: kern[k]["ms"])
     apply_ms, apply_calls = timers["CombinedPreconditioner/apply"]
     apply_bytes = stats["trisolve_fwd"] + stats["trisolve_bwd"] + stats["restrict"] + stats["prolong"] + stats["coarse"]
+    traffic = None
+    try:
+        tr = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))
+        traffic = tr.get(f"ncell{a.ncell}_nsub{a.nsub}_{a.coarse}_nev{a.nev}_overlap{a.overlap}", {}).get(f"{dom}_kernel")
+    except OSError:
+        pass
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": a.warmup, "ms_per_step": ms_step,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
@@ -305,7 +327,7 @@ def run_b200(a):
         "e2e": {"value": n / (t_e2e / a.steps) / 1e6, "unit": UNIT, "h2d_bytes_per_step": int(2 * 8 * ctx.n_own), "d2h_bytes_per_step": int(2 * 8 * ctx.n_own)},
         "gpu_launches": int(launches),
         "roofline": {"bound": "hbm", "kernel": f"{dom}_kernel", "achieved": kern[dom]["GBps"], "peak": peak, "unit": "GB/s",
-                     "frac": kern[dom]["GBps"] / peak if kern[dom]["GBps"] else None, "traffic": None, "peak_source": peak_src,
+                     "frac": kern[dom]["GBps"] / peak if kern[dom]["GBps"] else None, "traffic": traffic, "peak_source": peak_src,
                      "algorithmic_bytes_per_launch": stats[dom], "ms_per_launch": kern[dom]["ms"], "kernels": kern},
         "timers_ms_per_call": {k: (v[0] / max(v[1], 1)) for k, v in timers.items()},
         "clocks": clk.summary(),

@@ -105,3 +105,23 @@ def galerkin_matrix(A, subs, bases):
     Z = sp.coo_matrix((vals, (rows, cols)), shape=(n, int(off[-1]))).tocsr()
     A0 = (Z.T @ (A @ Z)).toarray()
     return A0, off, Z
+
+
+def galerkin_columns(A, subs, bases, mine):
+    """The columns of A0 = Z^T A Z that belong to the subdomains `mine` (a contiguous block): Z^T (A Z_mine)."""
+    _, off, Z = galerkin_matrix_operands(subs, bases, A.shape[0])
+    if not len(mine):
+        return np.zeros((int(off[-1]), 0))
+    c0, c1 = int(off[min(mine)]), int(off[max(mine) + 1])
+    return (Z.T @ (A @ Z[:, c0:c1])).toarray()
+
+
+def galerkin_matrix_operands(subs, bases, n):
+    ks = np.array([b.shape[1] for b in bases], dtype=np.int64)
+    off = np.concatenate(([0], np.cumsum(ks)))
+    rows = np.concatenate([np.repeat(s[:, None], b.shape[1], 1).ravel() for s, b in zip(subs, bases)])
+    cols = np.concatenate(
+        [np.tile(np.arange(o, o + b.shape[1]), (s.size, 1)).ravel() for s, b, o in zip(subs, bases, off[:-1])]
+    )
+    vals = np.concatenate([np.ascontiguousarray(b).ravel() for b in bases])
+    return ks, off, sp.coo_matrix((vals, (rows, cols)), shape=(n, int(off[-1]))).tocsc()

@@ -243,3 +243,170 @@ def solve_supernodal(F: SupernodalFactor, b):
     out = np.empty_like(y)
     out[F.perm] = y
     return out
+
+
+# ----------------------------------------------------------------------------- non-symmetric: supernodal LU
+@dataclass
+class SupernodalLU:
+    """Supernodal LU of a matrix with (symmetrised) pattern, no pivoting across supernodes.
+
+    Same symbolic fields as SupernodalFactor (super / pi / px / s, one row list shared by L and U^T).  `x` holds the panels
+    of L (column-major nrow x ncol, unit diagonal stored explicitly), `xu` the panels of U^T in the same layout (top block
+    = U_JJ^T, lower triangular with the pivots on its diagonal; rows below = U_{J,struct}^T).
+    """
+
+    n: int
+    perm: np.ndarray
+    super_: np.ndarray
+    pi: np.ndarray
+    px: np.ndarray
+    s: np.ndarray
+    x: np.ndarray
+    xu: np.ndarray
+
+    @property
+    def nsuper(self):
+        return self.super_.size - 1
+
+    def nnz_panels(self):
+        return int(self.x.size + self.xu.size)
+
+    def nnz_lower(self):  # entries one sweep streams (L incl. diagonal == U incl. diagonal)
+        c = np.diff(self.super_).astype(np.int64)
+        r = np.diff(self.pi) - c
+        return int((c * (c + 1) // 2 + r * c).sum())
+
+
+def _lu_nopivot(F11):
+    """Dense LU without pivoting, recursive blocked Doolittle: F11 = L U, L unit lower."""
+    c = F11.shape[0]
+    if c <= 48:
+        M = F11.copy()
+        for k in range(c):
+            piv = M[k, k]
+            if piv == 0.0:
+                raise np.linalg.LinAlgError("zero pivot in the subdomain LU (the restated setup does not pivot)")
+            M[k + 1 :, k] /= piv
+            M[k + 1 :, k + 1 :] -= np.outer(M[k + 1 :, k], M[k, k + 1 :])
+        return np.tril(M, -1) + np.eye(c), np.triu(M)
+    h = c // 2
+    L11, U11 = _lu_nopivot(F11[:h, :h])
+    U12 = _dtrsm(1.0, L11, F11[:h, h:], side=0, lower=1, diag=1)
+    L21 = _dtrsm(1.0, U11, F11[h:, :h], side=1, lower=0)
+    L22, U22 = _lu_nopivot(F11[h:, h:] - L21 @ U12)
+    L = np.zeros((c, c))
+    U = np.zeros((c, c))
+    L[:h, :h], L[h:, :h], L[h:, h:] = L11, L21, L22
+    U[:h, :h], U[:h, h:], U[h:, h:] = U11, U12, U22
+    return L, U
+
+
+def lu_supernodal(A, coords=None, leaf_size=32):
+    """Multifrontal LU of a square matrix on the nested-dissection tree of the pattern of A + A^T.
+
+    The reference factors non-symmetric subdomain matrices with UMFPACK through Dune::UMFPack
+    (/root/reference/dune/ddm/schwarz.hh:85-92, extern/dune-istl/dune/istl/umfpack.hh); UMFPACK is absent here, so the
+    factorisation is restated (same unsymmetric-multifrontal family; pivots stay inside a front's diagonal, which is safe
+    for the diffusion-dominated DG matrices this path is used for).
+    """
+    n = A.shape[0]
+    S = (abs(A) + abs(A).T).tocsr()
+    perm, first = nested_dissection(S, coords, leaf_size)
+    nsuper = first.size - 1
+    Ap = A.tocsr()[perm][:, perm]
+    Sp = S[perm][:, perm].tocsr()
+    Sp.sort_indices()
+    Ac = Ap.tocsc()  # columns of A: U^T panels are gathered from the rows, L panels from the columns
+    Ac.sort_indices()
+    Ar = Ap.tocsr()
+    Ar.sort_indices()
+    indptr, indices = Sp.indptr, Sp.indices
+    col2super = np.repeat(np.arange(nsuper), np.diff(first))
+    structs: list[np.ndarray] = [None] * nsuper  # type: ignore
+    parent = np.full(nsuper, -1, dtype=np.int64)
+    pending: list[list[int]] = [[] for _ in range(nsuper)]
+    for J in range(nsuper):
+        f, l = first[J], first[J + 1]
+        pieces = [indices[indptr[f] : indptr[l]]]
+        for c in pending[J]:
+            pieces.append(structs[c])
+        allidx = np.concatenate(pieces)
+        st = np.unique(allidx[allidx >= l])
+        structs[J] = st
+        if st.size:
+            parent[J] = col2super[st[0]]
+            pending[parent[J]].append(J)
+    ncol = np.diff(first)
+    nrow = ncol + np.array([s.size for s in structs], dtype=np.int64)
+    pi = np.concatenate(([0], np.cumsum(nrow))).astype(np.int64)
+    px = np.concatenate(([0], np.cumsum(nrow * ncol))).astype(np.int64)
+    s = np.empty(pi[-1], dtype=np.int32)
+    x = np.empty(px[-1], dtype=np.float64)
+    xu = np.empty(px[-1], dtype=np.float64)
+    loc = np.zeros(n, dtype=np.int64)
+    updates: dict[int, np.ndarray] = {}
+    for J in range(nsuper):
+        f, l = int(first[J]), int(first[J + 1])
+        c = l - f
+        st = structs[J]
+        m = c + st.size
+        idx = np.concatenate((np.arange(f, l), st))
+        s[pi[J] : pi[J + 1]] = idx
+        loc[idx] = np.arange(m)
+        F = np.zeros((m, m))
+        # columns f..l-1 of A (rows >= f) and rows f..l-1 of A (columns >= f)
+        lo, hi = Ac.indptr[f], Ac.indptr[l]
+        rows = Ac.indices[lo:hi]
+        cols = np.repeat(np.arange(c), np.diff(Ac.indptr[f : l + 1]))
+        keep = rows >= f
+        F[loc[rows[keep]], cols[keep]] = Ac.data[lo:hi][keep]
+        lo, hi = Ar.indptr[f], Ar.indptr[l]
+        cols2 = Ar.indices[lo:hi]
+        rows2 = np.repeat(np.arange(c), np.diff(Ar.indptr[f : l + 1]))
+        keep = cols2 >= l
+        F[rows2[keep], loc[cols2[keep]]] = Ar.data[lo:hi][keep]
+        for ch in pending[J]:
+            U = updates.pop(ch)
+            p = loc[structs[ch]]
+            F[np.ix_(p, p)] += U
+        L11, U11 = _lu_nopivot(F[:c, :c])
+        pl = np.empty((m, c), order="F")
+        pu = np.empty((m, c), order="F")
+        pl[:c] = L11
+        pu[:c] = U11.T
+        if m > c:
+            L21 = _dtrsm(1.0, U11, F[c:, :c], side=1, lower=0)  # X U11 = F21
+            U12 = _dtrsm(1.0, L11, F[:c, c:], side=0, lower=1, diag=1)  # L11 X = F12
+            pl[c:] = L21
+            pu[c:] = U12.T
+            if parent[J] >= 0:
+                updates[J] = F[c:, c:] - L21 @ U12
+        x[px[J] : px[J + 1]] = pl.ravel(order="F")
+        xu[px[J] : px[J + 1]] = pu.ravel(order="F")
+    return SupernodalLU(n=n, perm=perm.astype(np.int32), super_=first.astype(np.int32), pi=pi, px=px, s=s, x=x, xu=xu)
+
+
+def solve_supernodal_lu(F: SupernodalLU, b):
+    """Reference CPU solve with the LU factor (setup checks only)."""
+    y = np.asarray(b, dtype=np.float64)[F.perm].copy()
+    ns = F.nsuper
+    for J in range(ns):
+        f, l = F.super_[J], F.super_[J + 1]
+        c = l - f
+        rows = F.s[F.pi[J] : F.pi[J + 1]]
+        P = F.x[F.px[J] : F.px[J + 1]].reshape((rows.size, c), order="F")
+        y[f:l] = sla.solve_triangular(P[:c], y[f:l], lower=True, unit_diagonal=True, check_finite=False)
+        if rows.size > c:
+            y[rows[c:]] -= P[c:] @ y[f:l]
+    for J in range(ns - 1, -1, -1):
+        f, l = F.super_[J], F.super_[J + 1]
+        c = l - f
+        rows = F.s[F.pi[J] : F.pi[J + 1]]
+        P = F.xu[F.px[J] : F.px[J + 1]].reshape((rows.size, c), order="F")
+        t = y[f:l]
+        if rows.size > c:
+            t = t - P[c:].T @ y[rows[c:]]
+        y[f:l] = sla.solve_triangular(P[:c], t, lower=True, trans="T", check_finite=False)
+    out = np.empty_like(y)
+    out[F.perm] = y
+    return out

@@ -109,8 +109,13 @@ def _sub_job(i):
 
 
 def build(coords, cells, Ke, dirichlet, rhs, cell_part, nsub, overlap=2, pou_kind="distance", shrink=0,
-          coarse="geneo", nev=16, shift=1e-3, eig_tol=1e-5, leaf_size=32, workers=None, meta=None):
-    """Generic pipeline from an element-wise description to SetupProducts."""
+          coarse="geneo", nev=16, shift=1e-3, eig_tol=1e-5, leaf_size=32, workers=None, meta=None, only=None, gather=None):
+    """Generic pipeline from an element-wise description to SetupProducts.
+
+    only / gather: with several processes (one per GPU) every process factors and builds the coarse basis of its own
+    subdomains `only` (the reference does the same: one rank, one subdomain) and `gather(obj) -> [obj of rank 0, ...]`
+    exchanges the bases and the column blocks of the Galerkin matrix (the reference's neighbour exchange and
+    gatherMatrixFromRows, galerkin_preconditioner.hh:246-328).  Factors of other ranks' subdomains stay None."""
     import time
 
     verbose = bool(os.environ.get("DDM_SETUP_VERBOSE"))
@@ -138,19 +143,26 @@ def build(coords, cells, Ke, dirichlet, rhs, cell_part, nsub, overlap=2, pou_kin
     _G.clear()
     _G.update(A=A, subs=subs, coords=coords, cells=cells, Ke=Ke, dirichlet=dirichlet, shared=shared, pou=pou,
               coarse=coarse, nev=nev, shift=shift, eig_tol=eig_tol, leaf_size=leaf_size)
-    workers = workers or min(nsub, os.cpu_count() or 1)
+    todo = list(range(nsub)) if only is None else list(only)
+    workers = workers or min(max(len(todo), 1), os.cpu_count() or 1)
     factors = [None] * nsub
     Z = [None] * nsub
-    if workers > 1:
+    if workers > 1 and len(todo) > 1:
         with mp.get_context("fork").Pool(workers) as pool:
-            for i, F, Zi in pool.imap_unordered(_sub_job, range(nsub)):
+            for i, F, Zi in pool.imap_unordered(_sub_job, todo):
                 factors[i], Z[i] = F, Zi
     else:
-        for i in range(nsub):
+        for i in todo:
             _, factors[i], Z[i] = _sub_job(i)
     _G.clear()
     tick("factor + coarse basis")
-    A0, off, _ = coarse_mod.galerkin_matrix(A, subs, Z)
+    if gather is None:
+        A0, off, _ = coarse_mod.galerkin_matrix(A, subs, Z)
+    else:
+        for part in gather({i: Z[i] for i in todo}):
+            for i, Zi in part.items():
+                Z[i] = Zi
+        A0 = np.hstack(gather(coarse_mod.galerkin_columns(A, subs, Z, todo)))
     tick("galerkin")
     m = dict(meta or {})
     m.update(nsub=nsub, overlap=overlap, pou=pou_kind, coarse=coarse, nev=nev, n=int(n), N0=int(A0.shape[0]))

@@ -87,6 +87,44 @@ void oracle_super_solve(int32_t n, int32_t nsuper, const int32_t *super, const i
     for (int32_t k = 0; k < n; ++k) out[perm[k]] = y[k];
 }
 
+/* One subdomain solve with a supernodal LU factor (non-symmetric A_i): Dune::UMFPack::apply
+ * (/root/reference/extern/dune-istl/dune/istl/umfpack.hh, selected at /root/reference/dune/ddm/schwarz.hh:85-92) calls
+ * umfpack_dl_solve(UMFPACK_A): permute, forward solve with unit-lower L, backward solve with U, un-permute.  xl holds
+ * the L panels, xu the panels of U^T in the same layout (diagonal block = U_JJ^T, lower triangular). */
+void oracle_super_solve_lu(int32_t n, int32_t nsuper, const int32_t *super, const int64_t *pi, const int64_t *px,
+                           const int32_t *s, const double *xl, const double *xu, const int32_t *perm, const double *b,
+                           double *out, double *work /* n */)
+{
+    double *y = work;
+    for (int32_t k = 0; k < n; ++k) y[k] = b[perm[k]];
+    for (int32_t J = 0; J < nsuper; ++J) {
+        const int32_t f = super[J], c = super[J + 1] - f;
+        const int64_t m = pi[J + 1] - pi[J];
+        const double *P = xl + px[J];
+        const int32_t *rows = s + pi[J];
+        for (int32_t j = 0; j < c; ++j) {
+            const double yj = y[f + j]; /* unit diagonal */
+            const double *colj = P + (int64_t)j * m;
+            for (int32_t i = j + 1; i < c; ++i) y[f + i] -= colj[i] * yj;
+            for (int64_t i = c; i < m; ++i) y[rows[i]] -= colj[i] * yj;
+        }
+    }
+    for (int32_t J = nsuper - 1; J >= 0; --J) {
+        const int32_t f = super[J], c = super[J + 1] - f;
+        const int64_t m = pi[J + 1] - pi[J];
+        const double *P = xu + px[J]; /* column j of the panel = row j of U */
+        const int32_t *rows = s + pi[J];
+        for (int32_t j = c - 1; j >= 0; --j) {
+            const double *colj = P + (int64_t)j * m;
+            double acc = y[f + j];
+            for (int64_t i = c; i < m; ++i) acc -= colj[i] * y[rows[i]];
+            for (int32_t i = j + 1; i < c; ++i) acc -= colj[i] * y[f + i];
+            y[f + j] = acc / colj[j];
+        }
+    }
+    for (int32_t k = 0; k < n; ++k) out[perm[k]] = y[k];
+}
+
 /* SchwarzPreconditioner::apply, /root/reference/dune/ddm/schwarz.hh:115-149.
  * restricted != 0: x = sum_i R_i^T D_i A_i^{-1} R_i d ; else x = sum_i R_i^T A_i^{-1} R_i d.
  * The halo sums of addOwnerCopyToOwnerCopy are taken in ascending rank order. */
@@ -103,8 +141,12 @@ void oracle_schwarz_apply(const oracle_setup *S, int restricted, const double *d
             const int64_t o = S->sub_ptr[i], ni = S->sub_ptr[i + 1] - o;
             if (ni > cap) { free(dl); free(wk); cap = ni; dl = malloc(sizeof(double) * cap); wk = malloc(sizeof(double) * cap); }
             for (int64_t k = 0; k < ni; ++k) dl[k] = d[S->sub_dofs[o + k]]; /* restrict + copyOwnerToAll */
-            oracle_super_solve((int32_t)ni, S->nsuper[i], S->super[i], S->pi[i], S->px[i], S->s[i], S->x[i], S->perm[i], dl,
-                               xo + o, wk);
+            if (S->xu && S->xu[i])
+                oracle_super_solve_lu((int32_t)ni, S->nsuper[i], S->super[i], S->pi[i], S->px[i], S->s[i], S->x[i], S->xu[i],
+                                      S->perm[i], dl, xo + o, wk);
+            else
+                oracle_super_solve((int32_t)ni, S->nsuper[i], S->super[i], S->pi[i], S->px[i], S->s[i], S->x[i], S->perm[i], dl,
+                                   xo + o, wk);
             if (restricted && S->pou)
                 for (int64_t k = 0; k < ni; ++k) xo[o + k] *= S->pou[o + k];
         }
@@ -134,8 +176,25 @@ void oracle_coarse_apply(const oracle_setup *S, const double *d, double *x, int 
             d0[S->k_off[i] + k] = acc;
         }
     }
-    /* L L^T y = d0 */
+    /* A0 y = d0: dense LU with row swaps for a non-symmetric coarse matrix, else L L^T y = d0 */
     const double *L = S->A0chol;
+    if (S->A0lu) {
+        const double *M = S->A0lu;
+        for (int32_t i = 0; i < N0; ++i) {
+            const int32_t p = S->A0piv[i];
+            if (p != i) { const double t = d0[i]; d0[i] = d0[p]; d0[p] = t; }
+        }
+        for (int32_t i = 0; i < N0; ++i) {
+            double acc = d0[i];
+            for (int32_t j = 0; j < i; ++j) acc -= M[(int64_t)i * N0 + j] * d0[j];
+            d0[i] = acc;
+        }
+        for (int32_t i = N0 - 1; i >= 0; --i) {
+            double acc = d0[i];
+            for (int32_t j = i + 1; j < N0; ++j) acc -= M[(int64_t)i * N0 + j] * d0[j];
+            d0[i] = acc / M[(int64_t)i * N0 + i];
+        }
+    } else {
     for (int32_t i = 0; i < N0; ++i) {
         double acc = d0[i];
         for (int32_t j = 0; j < i; ++j) acc -= L[(int64_t)i * N0 + j] * d0[j];
@@ -145,6 +204,7 @@ void oracle_coarse_apply(const oracle_setup *S, const double *d, double *x, int 
         double acc = d0[i];
         for (int32_t j = i + 1; j < N0; ++j) acc -= L[(int64_t)j * N0 + i] * d0[j];
         d0[i] = acc / L[(int64_t)i * N0 + i];
+    }
     }
     memset(x, 0, sizeof(double) * (size_t)S->n);
     const int64_t tot = S->sub_ptr[S->nsub];

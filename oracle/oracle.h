@@ -29,6 +29,11 @@ typedef struct {
     const int64_t *rowptr;
     const int32_t *col;
     const double *val;
+    /* non-symmetric problems (NULL otherwise): panels of U^T per subdomain, same symbolic layout as x (which then holds
+     * the unit-lower L), and the dense coarse matrix as LAPACK getrf output (row-major L\\U, 0-based row swaps) */
+    const double **xu;
+    const double *A0lu;
+    const int32_t *A0piv;
 } oracle_setup;
 
 void oracle_spmv(int64_t n, const int64_t *rowptr, const int32_t *col, const double *val, const double *x, double *y,
@@ -36,6 +41,9 @@ void oracle_spmv(int64_t n, const int64_t *rowptr, const int32_t *col, const dou
 double oracle_dot(int64_t n, const double *x, const double *y);
 void oracle_super_solve(int32_t n, int32_t nsuper, const int32_t *super, const int64_t *pi, const int64_t *px,
                         const int32_t *s, const double *x, const int32_t *perm, const double *b, double *out, double *work);
+void oracle_super_solve_lu(int32_t n, int32_t nsuper, const int32_t *super, const int64_t *pi, const int64_t *px,
+                           const int32_t *s, const double *xl, const double *xu, const int32_t *perm, const double *b,
+                           double *out, double *work);
 void oracle_schwarz_apply(const oracle_setup *S, int restricted, const double *d, double *x, int nthreads);
 void oracle_coarse_apply(const oracle_setup *S, const double *d, double *x, int nthreads);
 void oracle_twolevel_apply(const oracle_setup *S, int restricted, int mode, int with_coarse, const double *d, double *x,

@@ -52,6 +52,7 @@ class _Setup(C.Structure):
         ("perm", C.POINTER(C.POINTER(C.c_int32))), ("z_ptr", C.POINTER(C.c_int64)), ("k_off", C.POINTER(C.c_int32)),
         ("Z", C.POINTER(C.c_double)), ("A0chol", C.POINTER(C.c_double)), ("rowptr", C.POINTER(C.c_int64)),
         ("col", C.POINTER(C.c_int32)), ("val", C.POINTER(C.c_double)),
+        ("xu", C.POINTER(C.POINTER(C.c_double))), ("A0lu", C.POINTER(C.c_double)), ("A0piv", C.POINTER(C.c_int32)),
     ]
 
 
@@ -78,7 +79,17 @@ class Oracle:
         if k["Z"].size == 0:
             k["Z"] = np.zeros(1)
         N0 = int(k["k_off"][-1])
-        k["A0chol"] = np.ascontiguousarray(np.linalg.cholesky(P.A0)) if N0 else np.zeros((1, 1))
+        self.nonsym = any(hasattr(F, "xu") for F in P.factors)
+        if self.nonsym:  # LU factors and a non-symmetric coarse matrix (restricted Schwarz + GMRES configurations)
+            xus = [np.ascontiguousarray(F.xu) for F in P.factors]
+            k["arr_xu"] = xus
+            k["ptr_xu"] = (C.POINTER(C.c_double) * ns)(*[_p(a, C.c_double) for a in xus])
+            k["A0chol"] = np.zeros((1, 1))
+            if N0:
+                lu, piv = sla.lu_factor(P.A0)
+                k["A0lu"], k["A0piv"] = np.ascontiguousarray(lu), np.ascontiguousarray(piv, dtype=np.int32)
+        else:
+            k["A0chol"] = np.ascontiguousarray(np.linalg.cholesky(P.A0)) if N0 else np.zeros((1, 1))
         k["rowptr"] = P.A.indptr.astype(np.int64)
         k["col"] = P.A.indices.astype(np.int32)
         k["val"] = P.A.data.astype(np.float64)
@@ -89,6 +100,10 @@ class Oracle:
         S.super, S.pi, S.px, S.s, S.x, S.perm = (k["ptr_super_"], k["ptr_pi"], k["ptr_px"], k["ptr_s"], k["ptr_x"], k["ptr_perm"])
         S.z_ptr, S.k_off, S.Z, S.A0chol = _p(k["z_ptr"], C.c_int64), _p(k["k_off"], C.c_int32), _p(k["Z"], C.c_double), _p(k["A0chol"], C.c_double)
         S.rowptr, S.col, S.val = _p(k["rowptr"], C.c_int64), _p(k["col"], C.c_int32), _p(k["val"], C.c_double)
+        if self.nonsym:
+            S.xu = k["ptr_xu"]
+            if N0:
+                S.A0lu, S.A0piv = _p(k["A0lu"], C.c_double), _p(k["A0piv"], C.c_int32)
         self.S = S
         self.N0 = N0
 
@@ -108,6 +123,11 @@ class Oracle:
         F = self.P.factors[i]
         out, wk = np.empty(F.n), np.empty(F.n)
         b = np.ascontiguousarray(b, dtype=np.float64)
+        if hasattr(F, "xu"):
+            lib().oracle_super_solve_lu(C.c_int32(F.n), C.c_int32(F.nsuper), _p(F.super_, C.c_int32), _p(F.pi, C.c_int64), _p(F.px, C.c_int64),
+                                        _p(F.s, C.c_int32), _p(F.x, C.c_double), _p(F.xu, C.c_double), _p(F.perm, C.c_int32),
+                                        _p(b, C.c_double), _p(out, C.c_double), _p(wk, C.c_double))
+            return out
         lib().oracle_super_solve(C.c_int32(F.n), C.c_int32(F.nsuper), _p(F.super_, C.c_int32), _p(F.pi, C.c_int64), _p(F.px, C.c_int64),
                                  _p(F.s, C.c_int32), _p(F.x, C.c_double), _p(F.perm, C.c_int32), _p(b, C.c_double), _p(out, C.c_double), _p(wk, C.c_double))
         return out

@@ -1,0 +1,56 @@
+"""Setup sharded over processes (bench.py with N > 1): every rank factors and builds the coarse basis of its own subdomains,
+bases and Galerkin columns are exchanged over gloo; the assembled products must equal the single-process setup."""
+import os
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+
+WORKER = r"""
+import os, sys, pickle
+sys.path.insert(0, os.path.join({root!r}, "dune-ddm_b200"))
+import numpy as np, torch.distributed as dist
+from ddm_b200.setup import problem
+from ddm_b200 import partition
+dist.init_process_group("gloo", init_method="tcp://127.0.0.1:{port}", rank=int(sys.argv[1]), world_size=2)
+rank, world = dist.get_rank(), dist.get_world_size()
+def gather(obj):
+    out = [None] * world
+    dist.all_gather_object(out, obj)
+    return out
+a, b = partition.sub_ranges(6, world)[rank]
+P = problem.unitcube_p1(10, 6, overlap=2, nev=4, workers=1, only=range(a, b), gather=gather)
+have = [i for i, F in enumerate(P.factors) if F is not None]
+pickle.dump(dict(A0=P.A0, Z=P.Z, have=have, x={{i: P.factors[i].x for i in have}}), open(sys.argv[2], "wb"))
+dist.destroy_process_group()
+"""
+
+
+@pytest.mark.timeout(300)
+def test_sharded_setup_equals_single_process(tmp_path):
+    import pickle
+    import socket
+
+    from ddm_b200.setup import problem
+
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        port = s.getsockname()[1]
+    script = tmp_path / "worker.py"
+    script.write_text(WORKER.format(root=os.path.dirname(HERE), port=port))
+    outs = [str(tmp_path / f"r{r}.pkl") for r in range(2)]
+    procs = [subprocess.Popen([sys.executable, str(script), str(r), outs[r]]) for r in range(2)]
+    for p in procs:
+        assert p.wait(timeout=280) == 0
+    P = problem.unitcube_p1(10, 6, overlap=2, nev=4, workers=1)
+    R = [pickle.load(open(o, "rb")) for o in outs]
+    assert R[0]["have"] == [0, 1, 2] and R[1]["have"] == [3, 4, 5]
+    for r in R:
+        assert np.allclose(r["A0"], P.A0, rtol=0, atol=1e-12 * np.abs(P.A0).max())
+        for i in range(6):
+            assert np.array_equal(r["Z"][i], P.Z[i])
+        for i in r["have"]:
+            assert np.array_equal(r["x"][i], P.factors[i].x)
