@@ -108,6 +108,9 @@ struct SubFactor {
     std::vector<int64_t> below_off; // offset of its first below-row tile (behind the diagonal block's tiles)
     std::vector<int64_t> row_off;   // offset of the supernode's row targets in `rowidx`
     double *panel = nullptr;        // device: tiles of [D^{-1}; -Lt] per supernode (trisolve.cuh)
+    double *panelU = nullptr;       // LU factors: tiles of -Ut^T (below rows only), read by the backward sweep
+    std::vector<int64_t> ubelow_off;
+    bool lu = false;
     int32_t *rowidx = nullptr;      // device: absolute WX offsets, filled at finalize
     std::vector<int32_t> rows_host; // -1 padding, -2-k = X position k (diagonal rows), >= 0 W position (below rows)
     int64_t panel_doubles = 0, nnz_lower = 0;
@@ -254,6 +257,7 @@ extern "C" int ddm_ctx_create(int device, ddm_ctx **out)
 static void free_factor(SubFactor &f)
 {
     cudaFree(f.panel);
+    cudaFree(f.panelU);
     cudaFree(f.rowidx);
     f = SubFactor();
 }
@@ -437,8 +441,29 @@ static inline int64_t diag_tile_off(int32_t cw, int32_t c)
     return off;
 }
 
-extern "C" int ddm_upload_factor(ddm_ctx *c, int32_t sub, int32_t n, int32_t nsuper, const int32_t *super, const int64_t *pi,
-                                 const int64_t *px, const int32_t *s, const double *x, const int32_t *perm)
+// Inverse of a cw x cw lower-triangular block stored in the first cw rows of a column-major panel with leading dimension m;
+// out(i, j) at out[j*cw + i].  Returns false on a zero pivot.
+static bool inv_lower(const double *Pn, int64_t m, int cw, double *out)
+{
+    auto Lkk = [&](int a, int b) { return Pn[(int64_t)b * m + a]; };
+    for (int j = 0; j < cw; ++j) {
+        const double djj = Lkk(j, j);
+        if (djj == 0.0 || !std::isfinite(djj)) return false;
+        out[(int64_t)j * cw + j] = 1.0 / djj;
+        for (int i = j + 1; i < cw; ++i) {
+            double acc = 0.0;
+            for (int k = j; k < i; ++k) acc += Lkk(i, k) * out[(int64_t)j * cw + k];
+            out[(int64_t)j * cw + i] = -acc / Lkk(i, i);
+        }
+    }
+    return true;
+}
+
+// x: panels of L (LL^T: the Cholesky factor; LU: unit lower L with its diagonal stored), xu: NULL for LL^T, else the panels
+// of U^T in the same layout.  Block form used by the sweeps:  A = Lt D Ut,  Lt_below = L_below L_JJ^{-1},
+// Ut_below^T = U_below^T U_JJ^{-T},  D_J = L_JJ U_JJ  (U = L^T in the symmetric case).
+static int upload_factor_impl(ddm_ctx *c, int32_t sub, int32_t n, int32_t nsuper, const int32_t *super, const int64_t *pi,
+                              const int64_t *px, const int32_t *s, const double *x, const double *xu, const int32_t *perm)
 {
     CU(cudaSetDevice(c->device));
     if (sub < 0 || sub >= c->nsub) return fail("factor for subdomain %d, but %d are hosted", sub, c->nsub);
@@ -446,6 +471,10 @@ extern "C" int ddm_upload_factor(ddm_ctx *c, int32_t sub, int32_t n, int32_t nsu
     SubFactor &F = c->fac[sub];
     if (F.present) free_factor(F);
     F.n = n;
+    F.lu = xu != nullptr;
+    const bool lu = F.lu;
+    F.ubelow_off.assign(nsuper, 0);
+    int64_t utile_doubles = 0;
     F.perm.assign(perm, perm + n);
     F.col0.resize(nsuper);
     F.cw.resize(nsuper);
@@ -454,12 +483,12 @@ extern "C" int ddm_upload_factor(ddm_ctx *c, int32_t sub, int32_t n, int32_t nsu
     F.below_off.resize(nsuper);
     F.row_off.resize(nsuper);
     std::vector<int32_t> col2super(n, -1);
-    std::vector<ConvTile> conv;
+    std::vector<ConvTile> conv, convU;
     std::vector<double> aux;  // small supernodes: Linv and Dinv blocks; wide supernodes: device-side work space behind it
     int64_t tile_doubles = 0, nrows_tot = 0, aux_wide = 0;
     struct Wide {
         int32_t J;
-        int64_t linv, dinv;  // offsets in aux (device)
+        int64_t linv, dinv, tinv;  // offsets in aux (device)
     };
     std::vector<Wide> wide;
     // pass 1: layout, row lists, small-supernode inverses on the host
@@ -480,40 +509,37 @@ extern "C" int ddm_upload_factor(ddm_ctx *c, int32_t sub, int32_t n, int32_t nsu
         for (int32_t r = 0; r < Rd * 32; ++r) F.rows_host.push_back(r < cw ? -2 - (f + r) : -1);  // encoded: -2-k = X position k
         for (int32_t r = 0; r < Rb * 32; ++r) F.rows_host.push_back(r < nb ? s[pi[J] + cw + r] : -1);
         // diagonal block: one full tile (cw <= 32) or the lower-triangular tiles of the symmetric inverse, chunk by chunk
-        const int64_t diag_doubles = cw <= 32 ? (int64_t)32 * cw : diag_tile_off(cw, Rd) ;
+        // (LU: the inverse diagonal block is not symmetric, wide supernodes keep it as Rd full row tiles)
+        const int64_t diag_doubles = cw <= 32 ? (int64_t)32 * cw : lu ? (int64_t)Rd * 32 * cw : diag_tile_off(cw, Rd);
         F.below_off[J] = tile_doubles + diag_doubles;
         tile_doubles += diag_doubles + (int64_t)Rb * 32 * cw;
+        F.ubelow_off[J] = utile_doubles;
+        if (lu) utile_doubles += (int64_t)Rb * 32 * cw;
         nrows_tot += (int64_t)(Rd + Rb) * 32;
     }
-    // aux layout: [small-supernode Linv | small-supernode Dinv | wide work space]
-    std::vector<int64_t> linv_off(nsuper, -1), dinv_off(nsuper, -1);
+    // aux layout: per small supernode [Linv | Dinv | (LU) Tinv, T = U_JJ^T], then the wide supernodes' work space
+    std::vector<int64_t> linv_off(nsuper, -1), dinv_off(nsuper, -1), tinv_off(nsuper, -1);
     for (int32_t J = 0; J < nsuper; ++J) {
         const int32_t cw = F.cw[J];
         if (cw > 32) continue;
         const int64_t m = pi[J + 1] - pi[J];
-        const double *Pn = x + px[J];
         const int64_t lo = (int64_t)aux.size();
-        aux.resize(lo + 2 * (size_t)cw * cw, 0.0);
-        double *Li = aux.data() + lo, *Di = Li + (size_t)cw * cw;
+        aux.resize(lo + (lu ? 3 : 2) * (size_t)cw * cw, 0.0);
+        double *Li = aux.data() + lo, *Di = Li + (size_t)cw * cw, *Ti = lu ? Di + (size_t)cw * cw : Li;
         linv_off[J] = lo;
         dinv_off[J] = lo + (int64_t)cw * cw;
-        auto Lkk = [&](int a, int b) { return Pn[(int64_t)b * m + a]; };
-        for (int j = 0; j < cw; ++j) {
-            const double djj = Lkk(j, j);
-            if (!(djj > 0.0)) return fail("factor of subdomain %d has a non-positive pivot", sub);
-            Li[(int64_t)j * cw + j] = 1.0 / djj;
-            for (int i = j + 1; i < cw; ++i) {
-                double acc = 0.0;
-                for (int k = j; k < i; ++k) acc += Lkk(i, k) * Li[(int64_t)j * cw + k];
-                Li[(int64_t)j * cw + i] = -acc / Lkk(i, i);
-            }
-        }
+        if (lu) tinv_off[J] = lo + 2 * (int64_t)cw * cw;
+        if (!inv_lower(x + px[J], m, cw, Li) || (lu && !inv_lower(xu + px[J], m, cw, Ti)))
+            return fail("factor of subdomain %d has a zero pivot", sub);
+        if (!lu)
+            for (int j = 0; j < cw; ++j)
+                if (!(x[px[J] + (int64_t)j * m + j] > 0.0)) return fail("factor of subdomain %d has a non-positive pivot", sub);
+        // D^{-1} = U_JJ^{-1} L_JJ^{-1} = Tinv^T Linv:  Dinv(a, b) = sum_{k >= max(a,b)} Tinv(k, a) Linv(k, b)
         for (int a = 0; a < cw; ++a)
-            for (int b = 0; b <= a; ++b) {
+            for (int b = 0; b < cw; ++b) {
                 double acc = 0.0;
-                for (int k = a; k < cw; ++k) acc += Li[(int64_t)a * cw + k] * Li[(int64_t)b * cw + k];
+                for (int k = std::max(a, b); k < cw; ++k) acc += Ti[(int64_t)a * cw + k] * Li[(int64_t)b * cw + k];
                 Di[(size_t)b * cw + a] = acc;
-                Di[(size_t)a * cw + b] = acc;
             }
     }
     const int64_t aux_small = (int64_t)aux.size();
@@ -524,9 +550,11 @@ extern "C" int ddm_upload_factor(ddm_ctx *c, int32_t sub, int32_t n, int32_t nsu
         wd.J = J;
         wd.linv = aux_small + aux_wide;
         wd.dinv = wd.linv + (int64_t)cw * cw;
-        aux_wide += 2 * (int64_t)cw * cw;
+        wd.tinv = wd.dinv + (int64_t)cw * cw;
+        aux_wide += (lu ? 3 : 2) * (int64_t)cw * cw;
         linv_off[J] = wd.linv;
         dinv_off[J] = wd.dinv;
+        tinv_off[J] = wd.tinv;
         wide.push_back(wd);
     }
     // conversion list
@@ -539,14 +567,16 @@ extern "C" int ddm_upload_factor(ddm_ctx *c, int32_t sub, int32_t n, int32_t nsu
                 ConvTile ct;
                 ct.w = (int16_t)std::min(32, cw - cc * 32);
                 ct.linv = 0;
-                if (r < Rd) {  // inverse diagonal block: lower-triangular tiles only (cw > 32), chunk-major
-                    if (cw > 32 && cc > r) continue;
+                if (r < Rd) {  // inverse diagonal block: lower-triangular tiles only (cw > 32, symmetric), chunk-major
+                    if (cw > 32 && cc > r && !lu) continue;
                     ct.kind = 1;
                     ct.srcsel = 1;
                     ct.ld = cw;
                     ct.src = dinv_off[J] + (int64_t)cc * 32 * cw + (int64_t)r * 32;
                     ct.nrows = std::min(32, cw - r * 32);
-                    ct.dst = cw <= 32 ? F.tile_off[J] : F.tile_off[J] + diag_tile_off(cw, cc) + (int64_t)(r - cc) * 32 * ct.w;
+                    ct.dst = cw <= 32 ? F.tile_off[J]
+                             : lu     ? F.tile_off[J] + (int64_t)r * 32 * cw + (int64_t)cc * 1024
+                                      : F.tile_off[J] + diag_tile_off(cw, cc) + (int64_t)(r - cc) * 32 * ct.w;
                 } else {
                     const int32_t rb = r - Rd;
                     ct.dst = F.below_off[J] + (int64_t)rb * 32 * cw + (int64_t)cc * 1024;
@@ -561,6 +591,11 @@ extern "C" int ddm_upload_factor(ddm_ctx *c, int32_t sub, int32_t n, int32_t nsu
                         ct.kind = 1;  // the raw panel already holds -Lt after the cuBLAS pass
                 }
                 conv.push_back(ct);
+                if (lu && r >= Rd) {  // the same tile of U^T (source: the U panels, inverse: Tinv) for the backward sweep
+                    ct.dst = F.ubelow_off[J] + (int64_t)(r - Rd) * 32 * cw + (int64_t)cc * 1024;
+                    if (cw <= 32) ct.linv = tinv_off[J];
+                    convU.push_back(ct);
+                }
             }
     }
     // parents and levels (supernodal elimination tree)
@@ -575,9 +610,10 @@ extern "C" int ddm_upload_factor(ddm_ctx *c, int32_t sub, int32_t n, int32_t nsu
         if (F.parent[J] >= 0) F.level[F.parent[J]] = std::max(F.level[F.parent[J]], F.level[J] + 1);
     F.panel_doubles = tile_doubles;
     // device: raw panels + aux -> tiles
-    double *raw = nullptr, *daux = nullptr;
-    ConvTile *dconv = nullptr;
+    double *raw = nullptr, *rawU = nullptr, *daux = nullptr;
+    ConvTile *dconv = nullptr, *dconvU = nullptr;
     CK(dev_upload(&raw, x, (size_t)px[nsuper]));
+    if (lu) CK(dev_upload(&rawU, xu, (size_t)px[nsuper]));
     CU(cudaMalloc((void **)&daux, sizeof(double) * std::max<int64_t>(1, aux_small + aux_wide)));
     if (aux_small) CU(cudaMemcpy(daux, aux.data(), sizeof(double) * aux_small, cudaMemcpyHostToDevice));
     if (!wide.empty()) {
@@ -595,8 +631,19 @@ extern "C" int ddm_upload_factor(ddm_ctx *c, int32_t sub, int32_t n, int32_t nsu
             LAUNCH(c, set_identity_kernel, nblocks(cw), 256, cw, Li);
             if (cublasDtrsm(c->blas, CUBLAS_SIDE_LEFT, CUBLAS_FILL_MODE_LOWER, CUBLAS_OP_N, CUBLAS_DIAG_NON_UNIT, cw, cw, &one, L11, (int)m, Li, cw) != CUBLAS_STATUS_SUCCESS)
                 return fail("cublasDtrsm (Linv) failed");
-            // Dinv = Linv^T Linv
-            if (cublasDgemm(c->blas, CUBLAS_OP_T, CUBLAS_OP_N, cw, cw, cw, &one, Li, cw, Li, cw, &zero, Di, cw) != CUBLAS_STATUS_SUCCESS)
+            double *Ti = Li;  // T = U_JJ^T (lower); symmetric case: T = L_JJ
+            if (lu) {
+                Ti = daux + wd.tinv;
+                double *T11 = rawU + px[wd.J];
+                LAUNCH(c, set_identity_kernel, nblocks(cw), 256, cw, Ti);
+                if (cublasDtrsm(c->blas, CUBLAS_SIDE_LEFT, CUBLAS_FILL_MODE_LOWER, CUBLAS_OP_N, CUBLAS_DIAG_NON_UNIT, cw, cw, &one, T11, (int)m, Ti, cw) != CUBLAS_STATUS_SUCCESS)
+                    return fail("cublasDtrsm (Tinv) failed");
+                // below panel of U^T <- -U_below^T U_JJ^{-T}: solve X * T11 = -U_below^T in place
+                if (nb > 0 && cublasDtrsm(c->blas, CUBLAS_SIDE_RIGHT, CUBLAS_FILL_MODE_LOWER, CUBLAS_OP_N, CUBLAS_DIAG_NON_UNIT, nb, cw, &mone, T11, (int)m, T11 + cw, (int)m) != CUBLAS_STATUS_SUCCESS)
+                    return fail("cublasDtrsm (Ut) failed");
+            }
+            // Dinv = Tinv^T Linv (= Linv^T Linv in the symmetric case)
+            if (cublasDgemm(c->blas, CUBLAS_OP_T, CUBLAS_OP_N, cw, cw, cw, &one, Ti, cw, Li, cw, &zero, Di, cw) != CUBLAS_STATUS_SUCCESS)
                 return fail("cublasDgemm (Dinv) failed");
             // below panel <- -L_below L11^{-1}: solve X * L11 = -L_below in place
             if (nb > 0 && cublasDtrsm(c->blas, CUBLAS_SIDE_RIGHT, CUBLAS_FILL_MODE_LOWER, CUBLAS_OP_N, CUBLAS_DIAG_NON_UNIT, nb, cw, &mone, L11, (int)m, L11 + cw, (int)m) != CUBLAS_STATUS_SUCCESS)
@@ -609,14 +656,36 @@ extern "C" int ddm_upload_factor(ddm_ctx *c, int32_t sub, int32_t n, int32_t nsu
         const int64_t nt = (int64_t)conv.size();
         LAUNCH(c, convert_tiles_kernel, nblocks(nt * 32), 256, nt, dconv, raw, daux, F.panel);
     }
+    if (lu) {
+        CK(dev_upload(&dconvU, convU.data(), convU.size()));
+        CU(cudaMalloc((void **)&F.panelU, sizeof(double) * std::max<int64_t>(1, utile_doubles)));
+        if (!convU.empty()) {
+            const int64_t nt = (int64_t)convU.size();
+            LAUNCH(c, convert_tiles_kernel, nblocks(nt * 32), 256, nt, dconvU, rawU, daux, F.panelU);
+        }
+    }
     CU(cudaStreamSynchronize(c->s));
     CU(cudaGetLastError());
     cudaFree(raw);
+    cudaFree(rawU);
     cudaFree(daux);
     cudaFree(dconv);
+    cudaFree(dconvU);
     F.present = true;
     c->finalized = false;
     return 0;
+}
+
+extern "C" int ddm_upload_factor(ddm_ctx *c, int32_t sub, int32_t n, int32_t nsuper, const int32_t *super, const int64_t *pi,
+                                 const int64_t *px, const int32_t *s, const double *x, const int32_t *perm)
+{
+    return upload_factor_impl(c, sub, n, nsuper, super, pi, px, s, x, nullptr, perm);
+}
+extern "C" int ddm_upload_factor_lu(ddm_ctx *c, int32_t sub, int32_t n, int32_t nsuper, const int32_t *super, const int64_t *pi,
+                                    const int64_t *px, const int32_t *s, const double *xl, const double *xu, const int32_t *perm)
+{
+    if (!xu) return fail("ddm_upload_factor_lu needs the U panels");
+    return upload_factor_impl(c, sub, n, nsuper, super, pi, px, s, xl, xu, perm);
 }
 
 extern "C" int ddm_upload_coarse(ddm_ctx *c, const int32_t *k, const double *Z, int32_t N0, int32_t k_offset, const double *A0)
@@ -640,6 +709,46 @@ extern "C" int ddm_upload_coarse(ddm_ctx *c, const int32_t *k, const double *Z, 
     cusolverDnHandle_t h;
     if (cusolverDnCreate(&h) != CUSOLVER_STATUS_SUCCESS) return fail("cusolverDnCreate failed");
     cusolverDnSetStream(h, c->s);
+    bool symmetric = true;
+    for (int i = 0; i < N0 && symmetric; ++i)
+        for (int j = 0; j < i; ++j) {
+            const double a = A0[(size_t)i * N0 + j], b = A0[(size_t)j * N0 + i];
+            if (std::fabs(a - b) > 1e-12 * (std::fabs(a) + std::fabs(b))) {
+                symmetric = false;
+                break;
+            }
+        }
+    if (!symmetric) {
+        // Non-symmetric Galerkin matrix (convection, restricted bases): dense LU with partial pivoting.  The row-major A0
+        // is A0^T to cuSOLVER; solving A0^T X = I gives A0^{-T} column-major, i.e. A0^{-1} row-major, which is what
+        // dense_gemv_kernel streams.
+        int lw = 0, hinfo = 0;
+        cusolverDnDgetrf_bufferSize(h, N0, N0, c->A0inv, N0, &lw);
+        double *work = nullptr, *LU = nullptr;
+        int *info = nullptr, *ipiv = nullptr;
+        CU(cudaMalloc((void **)&work, sizeof(double) * std::max(1, lw)));
+        CU(cudaMalloc((void **)&LU, sizeof(double) * (size_t)N0 * N0));
+        CU(cudaMalloc((void **)&info, sizeof(int)));
+        CU(cudaMalloc((void **)&ipiv, sizeof(int) * N0));
+        CU(cudaMemcpyAsync(LU, c->A0inv, sizeof(double) * (size_t)N0 * N0, cudaMemcpyDeviceToDevice, c->s));
+        cusolverStatus_t st = cusolverDnDgetrf(h, N0, N0, LU, N0, work, ipiv, info);
+        CU(cudaMemcpyAsync(&hinfo, info, sizeof(int), cudaMemcpyDeviceToHost, c->s));
+        CU(cudaStreamSynchronize(c->s));
+        if (st != CUSOLVER_STATUS_SUCCESS || hinfo != 0) return fail("coarse matrix is singular (getrf info %d)", hinfo);
+        CU(cudaMemsetAsync(c->A0inv, 0, sizeof(double) * (size_t)N0 * N0, c->s));
+        LAUNCH(c, set_identity_kernel, nblocks(N0), 256, N0, c->A0inv);
+        st = cusolverDnDgetrs(h, CUBLAS_OP_N, N0, N0, LU, N0, ipiv, c->A0inv, N0, info);
+        CU(cudaMemcpyAsync(&hinfo, info, sizeof(int), cudaMemcpyDeviceToHost, c->s));
+        CU(cudaStreamSynchronize(c->s));
+        if (st != CUSOLVER_STATUS_SUCCESS || hinfo != 0) return fail("coarse inverse failed (getrs info %d)", hinfo);
+        cudaFree(work);
+        cudaFree(LU);
+        cudaFree(info);
+        cudaFree(ipiv);
+        cusolverDnDestroy(h);
+        c->finalized = false;
+        return 0;
+    }
     int lwork = 0, lwork2 = 0;
     cusolverDnDpotrf_bufferSize(h, CUBLAS_FILL_MODE_LOWER, N0, c->A0inv, N0, &lwork);
     cusolverDnDpotri_bufferSize(h, CUBLAS_FILL_MODE_LOWER, N0, c->A0inv, N0, &lwork2);
@@ -799,6 +908,17 @@ extern "C" int ddm_finalize(ddm_ctx *c)
                     if (below) ++nf;
                 }
             } else {
+                if (F.lu) {
+                    // non-symmetric inverse diagonal block: Rd full row tiles, cut like the below rows (kinds 7 / 9)
+                    if (ncc >= kGroup) {
+                        const int32_t ngc = (ncc + kGroup - 1) / kGroup;
+                        for (int32_t r = 0; r < Rd; ++r)
+                            for (int32_t g = 0; g < ngc; ++g) fkeys.push_back({F.level[J], i, J, 7, r, g});
+                    } else {
+                        const int32_t rpt = kGroup / ncc;
+                        for (int32_t r = 0; r < Rd; r += rpt) fkeys.push_back({F.level[J], i, J, 9, r, std::min(rpt, Rd - r)});
+                    }
+                } else
                 // symmetric inverse diagonal block: column chunk c, up to kGroup-1 tiles r >= c per task (filler work)
                 for (int32_t cc = 0; cc < ncc; ++cc)
                     for (int32_t r0 = cc; r0 < Rd; r0 += kGroup - 1) fkeys.push_back({F.level[J], i, J, 5, cc, r0});
@@ -851,16 +971,18 @@ extern "C" int ddm_finalize(ddm_ctx *c)
             t.ncc = 1;
             t.ntiles = (int16_t)k.b;
             t.w = t.wlast = (int16_t)cw;
-        } else if (k.kind == 0) {  // below row tile a, chunk group b
+        } else if (k.kind == 0 || k.kind == 7) {  // below (0) or diagonal (7, LU) row tile a, chunk group b
             const int32_t c0 = k.b * kGroup, c1 = std::min(ncc, c0 + kGroup);
-            t.tiles = F.panel + F.below_off[k.J] + (int64_t)k.a * 32 * cw + (int64_t)c0 * 1024;
-            t.rowidx = F.rowidx + F.row_off[k.J] + (int64_t)(Rd + k.a) * 32;
+            const int64_t base = k.kind == 0 ? F.below_off[k.J] : F.tile_off[k.J];
+            t.tiles = F.panel + base + (int64_t)k.a * 32 * cw + (int64_t)c0 * 1024;
+            t.rowidx = F.rowidx + F.row_off[k.J] + (int64_t)((k.kind == 0 ? Rd : 0) + k.a) * 32;
             t.vec = col_abs + c0 * 32;
             t.ncc = t.ntiles = (int16_t)(c1 - c0);
             t.wlast = (int16_t)std::min(32, cw - (c1 - 1) * 32);
-        } else if (k.kind == 4) {  // below row tiles a .. a+b, all chunks
-            t.tiles = F.panel + F.below_off[k.J] + (int64_t)k.a * 32 * cw;
-            t.rowidx = F.rowidx + F.row_off[k.J] + (int64_t)(Rd + k.a) * 32;
+        } else if (k.kind == 4 || k.kind == 9) {  // below (4) or diagonal (9, LU) row tiles a .. a+b, all chunks
+            const int64_t base = k.kind == 4 ? F.below_off[k.J] : F.tile_off[k.J];
+            t.tiles = F.panel + base + (int64_t)k.a * 32 * cw;
+            t.rowidx = F.rowidx + F.row_off[k.J] + (int64_t)((k.kind == 4 ? Rd : 0) + k.a) * 32;
             t.vec = col_abs;
             t.ncc = (int16_t)ncc;
             t.ntiles = (int16_t)(k.b * ncc);
@@ -886,7 +1008,7 @@ extern "C" int ddm_finalize(ddm_ctx *c)
         const int32_t r0 = k.b * kGroup, r1 = std::min(Rb, r0 + kGroup);
         const int32_t par = sn_base[k.sub] + F.parent[k.J];
         TriTask t;
-        t.tiles = F.panel + F.below_off[k.J] + (int64_t)r0 * 32 * cw + (int64_t)k.a * 1024;
+        t.tiles = (F.lu ? F.panelU + F.ubelow_off[k.J] : F.panel + F.below_off[k.J]) + (int64_t)r0 * 32 * cw + (int64_t)k.a * 1024;
         t.rowidx = F.rowidx + F.row_off[k.J] + (int64_t)(Rd + r0) * 32;
         t.vec = (int32_t)(P + c->sub_ptr[k.sub] + F.col0[k.J] + k.a * 32);
         t.stride = 32 * cw;

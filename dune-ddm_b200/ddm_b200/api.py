@@ -109,6 +109,16 @@ class Context:
                                            _p(pou, C.c_double)))
         for i in range(a, b):
             F = P.factors[i]
+            if hasattr(F, "xu"):  # non-symmetric subdomain matrix: LU factor (the reference's UMFPack branch, schwarz.hh:85-92)
+                check(lib.ddm_upload_factor_lu(self.h, C.c_int32(i - a), C.c_int32(F.n), C.c_int32(F.nsuper),
+                                               _p(np.ascontiguousarray(F.super_, dtype=np.int32), C.c_int32),
+                                               _p(np.ascontiguousarray(F.pi, dtype=np.int64), C.c_int64),
+                                               _p(np.ascontiguousarray(F.px, dtype=np.int64), C.c_int64),
+                                               _p(np.ascontiguousarray(F.s, dtype=np.int32), C.c_int32),
+                                               _p(np.ascontiguousarray(F.x, dtype=np.float64), C.c_double),
+                                               _p(np.ascontiguousarray(F.xu, dtype=np.float64), C.c_double),
+                                               _p(np.ascontiguousarray(F.perm, dtype=np.int32), C.c_int32)))
+                continue
             check(lib.ddm_upload_factor(self.h, C.c_int32(i - a), C.c_int32(F.n), C.c_int32(F.nsuper),
                                         _p(np.ascontiguousarray(F.super_, dtype=np.int32), C.c_int32),
                                         _p(np.ascontiguousarray(F.pi, dtype=np.int64), C.c_int64),

@@ -78,6 +78,8 @@ def products_to_arrays(P) -> dict:
         d[f"F{i}_s"] = np.asarray(F.s, dtype=np.int32)
         d[f"F{i}_x"] = np.asarray(F.x, dtype=np.float64)
         d[f"F{i}_perm"] = np.asarray(F.perm, dtype=np.int32)
+        if hasattr(F, "xu"):  # LU factor of a non-symmetric subdomain matrix
+            d[f"F{i}_xu"] = np.asarray(F.xu, dtype=np.float64)
     return d
 
 
@@ -103,7 +105,9 @@ def load_products(path):
         ni = int(sub_ptr[i + 1] - sub_ptr[i])
         Z.append(np.asfortranarray(d["Z"][zo : zo + ni * int(k[i])].reshape((ni, int(k[i])), order="F")))
         zo += ni * int(k[i])
-    factors = [factor.SupernodalFactor(n=subs[i].size, perm=d[f"F{i}_perm"], super_=d[f"F{i}_super"], pi=d[f"F{i}_pi"],
-                                       px=d[f"F{i}_px"], s=d[f"F{i}_s"], x=d[f"F{i}_x"]) for i in range(ns)]
+    factors = []
+    for i in range(ns):
+        kw = dict(n=subs[i].size, perm=d[f"F{i}_perm"], super_=d[f"F{i}_super"], pi=d[f"F{i}_pi"], px=d[f"F{i}_px"], s=d[f"F{i}_s"], x=d[f"F{i}_x"])
+        factors.append(factor.SupernodalLU(xu=d[f"F{i}_xu"], **kw) if f"F{i}_xu" in d else factor.SupernodalFactor(**kw))
     return SetupProducts(A=A, b=d["b"], owner=d["owner"], subs=subs, pou=pou, factors=factors, Z=Z, A0=d["A0"],
                          n_novlp=d["n_novlp"], meta=dict(n=n, nsub=ns, N0=int(d["A0"].shape[0])))

@@ -93,7 +93,7 @@ def _sub_job(i):
         Ai = A[s][:, s].tocsr()
         Ai.sort_indices()
         co = g["coords"][s] if g["coords"] is not None else None
-        F = factor.cholesky_supernodal(Ai, co, g["leaf_size"])
+        F = factor.cholesky_supernodal(Ai, co, g["leaf_size"]) if g["symmetric"] else factor.lu_supernodal(Ai, co, g["leaf_size"])
         kind = g["coarse"]
         dl = g["dirichlet"][s]
         if kind == "geneo":
@@ -109,7 +109,8 @@ def _sub_job(i):
 
 
 def build(coords, cells, Ke, dirichlet, rhs, cell_part, nsub, overlap=2, pou_kind="distance", shrink=0,
-          coarse="geneo", nev=16, shift=1e-3, eig_tol=1e-5, leaf_size=32, workers=None, meta=None, only=None, gather=None):
+          coarse="geneo", nev=16, shift=1e-3, eig_tol=1e-5, leaf_size=32, workers=None, meta=None, only=None, gather=None,
+          A_full=None, symmetric=True):
     """Generic pipeline from an element-wise description to SetupProducts.
 
     only / gather: with several processes (one per GPU) every process factors and builds the coarse basis of its own
@@ -127,7 +128,8 @@ def build(coords, cells, Ke, dirichlet, rhs, cell_part, nsub, overlap=2, pou_kin
         t0[0] = time.time()
 
     n = coords.shape[0]
-    A_full = fem.assemble(n, cells, Ke)
+    if A_full is None:  # continuous FE: assemble from the element matrices; DG passes its matrix (cells = DOFs per cell)
+        A_full = fem.assemble(n, cells, Ke)
     A = fem.eliminate_dirichlet(A_full, dirichlet)
     b = np.where(dirichlet, 0.0, rhs)
     tick("assemble")
@@ -142,7 +144,7 @@ def build(coords, cells, Ke, dirichlet, rhs, cell_part, nsub, overlap=2, pou_kin
         shared[s] += 1
     _G.clear()
     _G.update(A=A, subs=subs, coords=coords, cells=cells, Ke=Ke, dirichlet=dirichlet, shared=shared, pou=pou,
-              coarse=coarse, nev=nev, shift=shift, eig_tol=eig_tol, leaf_size=leaf_size)
+              coarse=coarse, nev=nev, shift=shift, eig_tol=eig_tol, leaf_size=leaf_size, symmetric=symmetric)
     todo = list(range(nsub)) if only is None else list(only)
     workers = workers or min(max(len(todo), 1), os.cpu_count() or 1)
     factors = [None] * nsub
@@ -165,7 +167,7 @@ def build(coords, cells, Ke, dirichlet, rhs, cell_part, nsub, overlap=2, pou_kin
         A0 = np.hstack(gather(coarse_mod.galerkin_columns(A, subs, Z, todo)))
     tick("galerkin")
     m = dict(meta or {})
-    m.update(nsub=nsub, overlap=overlap, pou=pou_kind, coarse=coarse, nev=nev, n=int(n), N0=int(A0.shape[0]))
+    m.update(nsub=nsub, overlap=overlap, pou=pou_kind, coarse=coarse, nev=nev, n=int(n), N0=int(A0.shape[0]), symmetric=bool(symmetric))
     return SetupProducts(A=A, b=b, owner=owner, subs=subs, pou=pou, factors=factors, Z=Z, A0=A0, coords=coords,
                          n_novlp=np.array([v.size for v in novlp], dtype=np.int64),
                          dirichlet=dirichlet, meta=m)
@@ -211,3 +213,17 @@ def unitcube_p1(ncell, nsub, **kw):
 def unitsquare_p1(ncell, nsub, **kw):
     coords, cells = mesh.structured_simplices((ncell,) * 2)
     return poisson_simplex(coords, cells, nsub, meta=dict(mesh=f"kuhn-{ncell}^2"), **kw)
+
+
+def convdiff_dg(ncell, nsub, overlap=1, **kw):
+    """Config C4: Q1-DG convection-diffusion on ncell^2 cells (examples/convectiondiffusiondg.{cc,hh,ini}): non-symmetric,
+    LU subdomain factors, coarse space = partition of unity times the template vectors {1, x, y, xy}
+    (dune/ddm/twolevel_schwarz.hh:47-51,107); meant for restricted Schwarz + multiplicative coarse + GMRES."""
+    from . import dg
+
+    A, rhs, coords, cell_dofs, cent = dg.assemble_cd_dg(ncell)
+    part = decomp.rcb_partition(cent, nsub)
+    dirichlet = np.zeros(A.shape[0], dtype=bool)  # boundary conditions are weak in DG
+    meta = dict(kw.pop("meta", {}), problem="convdiff-q1dg", dim=2, ncell=int(ncell))
+    kw.setdefault("coarse", "pou")
+    return build(coords, cell_dofs, None, dirichlet, rhs, part, nsub, overlap=overlap, meta=meta, A_full=A, symmetric=False, **kw)

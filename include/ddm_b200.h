@@ -91,10 +91,18 @@ int ddm_upload_decomposition(ddm_ctx *ctx, int32_t nsub, const int64_t *sub_ptr,
 int ddm_upload_factor(ddm_ctx *ctx, int32_t sub, int32_t n, int32_t nsuper, const int32_t *super, const int64_t *pi,
                       const int64_t *px, const int32_t *s, const double *x, const int32_t *perm);
 
+/* Non-symmetric subdomain matrices: LU factor of A_i in the same supernodal layout (one symbolic structure for L and U^T).
+ * Stands in for the numeric object of Dune::UMFPack, the solver the reference picks for non-symmetric problems
+ * (dune/ddm/schwarz.hh:85-92; extern/dune-istl/dune/istl/umfpack.hh: umfpack_dl_numeric / umfpack_dl_solve, whose L, U, P, Q
+ * umfpack_dl_get_numeric exports).  xl: panels of the unit-lower L (diagonal stored), xu: panels of U^T (top block = U_JJ^T,
+ * lower triangular, pivots on its diagonal); perm is applied to rows and columns alike. */
+int ddm_upload_factor_lu(ddm_ctx *ctx, int32_t sub, int32_t n, int32_t nsuper, const int32_t *super, const int64_t *pi,
+                         const int64_t *px, const int32_t *s, const double *xl, const double *xu, const int32_t *perm);
+
 /* Coarse space (dune/ddm/galerkin_preconditioner.hh:119-144,220-349): per hosted subdomain k[i]
  * basis vectors, Z = concatenation of column-major n_i x k[i] blocks (restr_vecs, :353), the
  * global coarse dimension N0, this context's first coarse index k_offset, and the dense
- * symmetric Galerkin matrix A0 (N0 x N0, replicated on every context). */
+ * Galerkin matrix A0 (N0 x N0 row-major, replicated on every context; symmetric positive definite -> Cholesky, otherwise LU). */
 int ddm_upload_coarse(ddm_ctx *ctx, const int32_t *k, const double *Z, int32_t N0, int32_t k_offset,
                       const double *A0);
 

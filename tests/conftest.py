@@ -26,3 +26,12 @@ def small2d():
     from ddm_b200.setup import problem
 
     return problem.unitsquare_p1(40, 16, overlap=2, nev=8, workers=1)
+
+
+@pytest.fixture(scope="session")
+def cd_dg():
+    """Config C4 at reduced size: Q1-DG convection-diffusion, 48^2 cells, 6 subdomains, overlap 1, LU factors,
+    POU x {1, x, y, xy} coarse space (non-symmetric A and A0)."""
+    from ddm_b200.setup import problem
+
+    return problem.convdiff_dg(48, 6, workers=1)
