@@ -132,6 +132,8 @@ struct ddm_ctx {
     int32_t *rowptr = nullptr, *col = nullptr;
     double *val = nullptr;
     int spmv_group = 8;
+    int block = 1;       // 1: scalar CSR, 3: 3x3 block CSR (rowptr/col index blocks, val holds 9 doubles per block)
+    int64_t nb_own = 0;  // block rows
     // decomposition
     int32_t nsub = 0;
     std::vector<int64_t> sub_ptr;
@@ -411,6 +413,35 @@ extern "C" int ddm_upload_operator(ddm_ctx *c, int64_t n_own, int64_t n_ghost, c
     c->stats["dot"] = 16.0 * n_own;
     c->stats["axpy"] = 24.0 * n_own;
     CU(cudaMallocHost((void **)&c->h_stage, sizeof(double) * std::max<int64_t>(1, 2 * n_own)));
+    return 0;
+}
+
+extern "C" int ddm_upload_operator_bcsr3(ddm_ctx *c, int64_t nb_own, int64_t nb_ghost, const int64_t *rowptr, const int32_t *col,
+                                         const double *val)
+{
+    CU(cudaSetDevice(c->device));
+    if (c->rowptr) return fail("operator already uploaded");
+    const int64_t nnzb = rowptr[nb_own];
+    if (9 * nnzb >= (int64_t)INT32_MAX) return fail("operator has %lld blocks; one GPU holds at most (2^31-1)/9", (long long)nnzb);
+    if (3 * (nb_own + nb_ghost) >= (int64_t)INT32_MAX) return fail("too many local DOFs");
+    c->block = 3;
+    c->nb_own = nb_own;
+    c->n_own = 3 * nb_own;
+    c->n_ghost = 3 * nb_ghost;
+    c->nloc = c->n_own + c->n_ghost;
+    c->nnz = 9 * nnzb;
+    std::vector<int32_t> rp(nb_own + 1);
+    for (int64_t i = 0; i <= nb_own; ++i) rp[i] = (int32_t)rowptr[i];
+    CK(dev_upload(&c->rowptr, rp.data(), rp.size()));
+    CK(dev_upload(&c->col, col, (size_t)nnzb));
+    CK(dev_upload(&c->val, val, (size_t)(9 * nnzb)));
+    const double mean = nb_own ? 9.0 * (double)nnzb / (double)nb_own : 9.0;
+    c->spmv_group = mean <= 40 ? 8 : mean <= 96 ? 16 : 32;
+    if (const char *e = getenv("DDM_SPMV_GROUP")) c->spmv_group = atoi(e);
+    c->stats["spmv"] = 76.0 * nnzb + 4.0 * (nb_own + 1) + 48.0 * nb_own;  // (72+4) nnzb + 4 (nb+1) + 48 nb
+    c->stats["dot"] = 16.0 * c->n_own;
+    c->stats["axpy"] = 24.0 * c->n_own;
+    CU(cudaMallocHost((void **)&c->h_stage, sizeof(double) * std::max<int64_t>(1, 2 * c->n_own)));
     return 0;
 }
 
@@ -1119,6 +1150,15 @@ static int spmv(ddm_ctx *c, double *x, double *y, double alpha, int mode)
     ScopedTimer tm(c, "Operator/apply");
     CK(halo_forward(c, x));
     const int G = c->spmv_group;
+    if (c->block == 3) {
+        const int gridb = nblocks(c->nb_own * G);
+        switch (G) {
+        case 8: LAUNCH(c, spmv_bcsr3_kernel<8>, gridb, 256, c->nb_own, c->rowptr, c->col, c->val, x, y, alpha, mode); break;
+        case 16: LAUNCH(c, spmv_bcsr3_kernel<16>, gridb, 256, c->nb_own, c->rowptr, c->col, c->val, x, y, alpha, mode); break;
+        default: LAUNCH(c, spmv_bcsr3_kernel<32>, gridb, 256, c->nb_own, c->rowptr, c->col, c->val, x, y, alpha, mode); break;
+        }
+        return 0;
+    }
     const int grid = nblocks(c->n_own * G);
     switch (G) {
     case 2: LAUNCH(c, spmv_csr_kernel<2>, grid, 256, c->n_own, c->rowptr, c->col, c->val, x, y, alpha, mode); break;

@@ -39,6 +39,45 @@ __global__ void __launch_bounds__(256) spmv_csr_kernel(int64_t n, const int32_t 
     }
 }
 
+// K1b  block-CSR SpMV with 3x3 blocks (BCRSMatrix<FieldMatrix<double,3,3>>, linear elasticity): same entry points as K1.
+// The 9*nblk values of a block row are one contiguous stream; G lanes walk it element by element (fully coalesced: lane t
+// reads value e = 9*first + t, t + G, ...), element e belongs to block e/9, row (e%9)/3, column e%3 of that block.  Each
+// lane keeps three partial sums (one per block row), reduced across the G lanes at the end.  Vectors are node-major
+// (BlockVector<FieldVector<double,3>>).
+template <int G>
+__global__ void __launch_bounds__(256) spmv_bcsr3_kernel(int64_t nb, const int32_t *__restrict__ rowptr,
+                                                         const int32_t *__restrict__ col, const double *__restrict__ val,
+                                                         const double *__restrict__ x, double *__restrict__ y, double alpha,
+                                                         int mode)
+{
+    const int64_t gtid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t row = gtid / G;
+    const int lane = (int)(gtid % G);
+    double a0 = 0.0, a1 = 0.0, a2 = 0.0;
+    if (row < nb) {
+        const int32_t b = rowptr[row], e9 = 9 * rowptr[row + 1];
+        for (int32_t e = 9 * b + lane; e < e9; e += G) {
+            const int32_t blk = e / 9, rem = e - 9 * blk, rr = rem / 3, cc = rem - 3 * rr;
+            const double p = val[e] * __ldg(x + 3 * (int64_t)col[blk] + cc);
+            a0 += rr == 0 ? p : 0.0;
+            a1 += rr == 1 ? p : 0.0;
+            a2 += rr == 2 ? p : 0.0;
+        }
+    }
+#pragma unroll
+    for (int o = G / 2; o > 0; o >>= 1) {
+        a0 += __shfl_xor_sync(kFull, a0, o, G);
+        a1 += __shfl_xor_sync(kFull, a1, o, G);
+        a2 += __shfl_xor_sync(kFull, a2, o, G);
+    }
+    if (row < nb && lane < 3) {
+        const double a = lane == 0 ? a0 : lane == 1 ? a1 : a2;
+        double *yp = y + 3 * row + lane;
+        if (mode == 0) *yp = a;
+        else *yp += alpha * a;
+    }
+}
+
 // ------------------------------------------------------------------------------------------------
 // K8/K9  vector updates and deterministic two-stage reductions (Krylov recurrences of
 // extern/dune-istl/dune/istl/solvers.hh:312-335; masked dot of owneroverlapcopy.hh:398-444).

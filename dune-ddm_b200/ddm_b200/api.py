@@ -97,8 +97,19 @@ class Context:
         if world > 1:
             uid = (C.c_uint8 * 128)(*unique_id)
             check(lib.ddm_comm_init(self.h, C.c_int(rank), C.c_int(world), uid))
-        check(lib.ddm_upload_operator(self.h, C.c_int64(S.n_own), C.c_int64(S.n_ghost), _p(S.rowptr, C.c_int64),
-                                      _p(S.col, C.c_int32), _p(S.val, C.c_double)))
+        if P.meta.get("block") == 3:  # node-major 3x3 blocks: BCRSMatrix<FieldMatrix<double,3,3>>
+            import scipy.sparse as sp
+
+            if S.n_own % 3 or S.n_ghost % 3 or (S.owned[::3] % 3).any() or (S.ghosts[::3] % 3).any():
+                raise DDMError("3x3 block operator: owned and ghost DOFs must come in whole nodes")
+            B = sp.csr_matrix((S.val, S.col, S.rowptr), shape=(S.n_own, S.n_own + S.n_ghost)).tobsr((3, 3))
+            B.sort_indices()
+            check(lib.ddm_upload_operator_bcsr3(self.h, C.c_int64(S.n_own // 3), C.c_int64(S.n_ghost // 3),
+                                                _p(B.indptr.astype(np.int64), C.c_int64), _p(B.indices.astype(np.int32), C.c_int32),
+                                                _p(np.ascontiguousarray(B.data, dtype=np.float64), C.c_double)))
+        else:
+            check(lib.ddm_upload_operator(self.h, C.c_int64(S.n_own), C.c_int64(S.n_ghost), _p(S.rowptr, C.c_int64),
+                                          _p(S.col, C.c_int32), _p(S.val, C.c_double)))
         self.n_own = S.n_own
         if world > 1:
             check(lib.ddm_upload_halo(self.h, C.c_int32(S.peers.size), _p(S.peers, C.c_int32), _p(S.send_ptr, C.c_int64),

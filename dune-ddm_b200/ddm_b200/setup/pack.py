@@ -70,6 +70,7 @@ def products_to_arrays(P) -> dict:
         k=np.array([z.shape[1] for z in P.Z], dtype=np.int32),
         Z=np.concatenate([z.ravel(order="F") for z in P.Z]).astype(np.float64) if ns else np.zeros(0),
         A0=np.ascontiguousarray(P.A0, dtype=np.float64),
+        block=np.array([int(P.meta.get("block", 1))], dtype=np.int64),
     )
     for i, F in enumerate(P.factors):
         d[f"F{i}_super"] = np.asarray(F.super_, dtype=np.int32)
@@ -110,4 +111,4 @@ def load_products(path):
         kw = dict(n=subs[i].size, perm=d[f"F{i}_perm"], super_=d[f"F{i}_super"], pi=d[f"F{i}_pi"], px=d[f"F{i}_px"], s=d[f"F{i}_s"], x=d[f"F{i}_x"])
         factors.append(factor.SupernodalLU(xu=d[f"F{i}_xu"], **kw) if f"F{i}_xu" in d else factor.SupernodalFactor(**kw))
     return SetupProducts(A=A, b=d["b"], owner=d["owner"], subs=subs, pou=pou, factors=factors, Z=Z, A0=d["A0"],
-                         n_novlp=d["n_novlp"], meta=dict(n=n, nsub=ns, N0=int(d["A0"].shape[0])))
+                         n_novlp=d["n_novlp"], meta=dict(n=n, nsub=ns, N0=int(d["A0"].shape[0]), block=int(d["block"][0]) if "block" in d else 1))

@@ -227,3 +227,24 @@ def convdiff_dg(ncell, nsub, overlap=1, **kw):
     meta = dict(kw.pop("meta", {}), problem="convdiff-q1dg", dim=2, ncell=int(ncell))
     kw.setdefault("coarse", "pou")
     return build(coords, cell_dofs, None, dirichlet, rhs, part, nsub, overlap=overlap, meta=meta, A_full=A, symmetric=False, **kw)
+
+
+def elasticity_box(gridsize=8, nsub=16, overlap=1, nev=12, **kw):
+    """Config C3: P1 linear elasticity on the 10 x 1 x 1.5 simplex box with steel bars in rubber
+    (examples/linearelasticity.cc:39-41, coefficient.lua), clamped at x = 0, gravity load, GenEO nev 12
+    (linearelasticity.ini:27-30).  DOFs are node-major: the operator is a 3x3 block-CSR matrix."""
+    from . import elasticity as el
+
+    g = int(gridsize)
+    shape = (10 * g, g, int(1.5 * g))
+    coords, cells = mesh.structured_simplices(shape, lengths=(10.0, 1.0, 1.5))
+    cent = coords[cells].mean(axis=1)
+    lam, mu = el.lame_bars(cent)
+    Ke, vol = el.p1_elasticity_element_matrices(coords, cells, lam, mu)
+    dcells = el.dof_cells(cells)
+    dcoords = np.repeat(coords, 3, axis=0)
+    dirichlet = np.repeat(coords[:, 0] < 1e-9, 3)
+    rhs = el.body_force(coords.shape[0], cells, vol)
+    part = decomp.rcb_partition(cent, nsub)
+    meta = dict(kw.pop("meta", {}), problem="elasticity-p1", dim=3, block=3, mesh=f"kuhn-{shape}")
+    return build(dcoords, dcells, Ke, dirichlet, rhs, part, nsub, overlap=overlap, nev=nev, meta=meta, **kw)

@@ -70,6 +70,12 @@ int ddm_comm_init(ddm_ctx *ctx, int rank, int nranks, const uint8_t nccl_unique_
 int ddm_upload_operator(ddm_ctx *ctx, int64_t n_own, int64_t n_ghost, const int64_t *rowptr, const int32_t *col,
                         const double *val);
 
+/* The same operator for Dune::BCRSMatrix<FieldMatrix<double,3,3>> (linear elasticity, examples/linearelasticity.hh): block
+ * rows of the owned nodes, block-column indices in local node numbering, 9 doubles per block (row-major).  Vectors are
+ * node-major (BlockVector<FieldVector<double,3>>): n_own = 3 nb_own, n_ghost = 3 nb_ghost scalar entries. */
+int ddm_upload_operator_bcsr3(ddm_ctx *ctx, int64_t nb_own, int64_t nb_ghost, const int64_t *rowptr, const int32_t *col,
+                              const double *val);
+
 /* Halo plan replacing the OwnerOverlapCopyCommunication interfaces
  * (extern/dune-istl/dune/istl/owneroverlapcopy.hh:311-387).  Ghost entries are stored grouped by
  * owning peer: ghosts of peers[p] occupy local indices n_own + recv_ptr[p] .. n_own + recv_ptr[p+1].

@@ -35,3 +35,12 @@ def cd_dg():
     from ddm_b200.setup import problem
 
     return problem.convdiff_dg(48, 6, workers=1)
+
+
+@pytest.fixture(scope="session")
+def elast():
+    """Config C3 at reduced size: P1 elasticity on the 10 x 1 x 1.5 box (30 x 3 x 4 cells), steel bars in rubber, clamped
+    at x = 0, 6 subdomains, overlap 1, GenEO nev 8; node-major DOFs (3x3 block operator)."""
+    from ddm_b200.setup import problem
+
+    return problem.elasticity_box(3, 6, nev=8, workers=1)
