@@ -39,6 +39,9 @@ def parse():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--ncell", type=int, default=int(os.environ.get("DDM_BENCH_NCELL", 112)), help="cells per unit length")
     ap.add_argument("--nsub", type=int, default=64, help="subdomains per GPU")
+    ap.add_argument("--workload", default="p1cube", choices=["p1cube", "q1cube"],
+                    help="p1cube: BASELINE.json configs[1] (default, the metric's configuration); q1cube: configs[4]'s family (structured Q1, "
+                         "27-point, channels coefficient, brick subdomains; --ncell cells per axis, nsub must be a cube; N=1 only)")
     ap.add_argument("--coarse", default="geneo", choices=["geneo", "pou"])
     ap.add_argument("--nev", type=int, default=16)
     ap.add_argument("--overlap", type=int, default=2)
@@ -54,6 +57,10 @@ def gpu_grid(n):
 
 
 def workload_name(a, world):
+    if a.workload == "q1cube":
+        p = round(a.nsub ** (1 / 3))
+        return (f"3D Q1 Poisson (27-point), channels coefficient 1e6, structured {a.ncell}^3 cells, {p}x{p}x{p} brick subdomains, "
+                f"overlap {a.overlap}, {a.coarse} coarse space nev {a.nev}, additive, CG 1e-8")
     g = gpu_grid(world)
     shape = tuple(a.ncell * k for k in g)
     return (f"3D P1 Poisson, islands coefficient (poisson_coefficient.lua), Kuhn mesh {shape[0]}x{shape[1]}x{shape[2]} cells, "
@@ -79,6 +86,11 @@ def build_problem(a, world, rank=None, gather=None):
 
 
 def _build_problem(a, world, fem, mesh, problem, **kw):
+    if a.workload == "q1cube":
+        p = round(a.nsub ** (1 / 3))
+        if p ** 3 != a.nsub or world != 1:
+            raise SystemExit("--workload q1cube needs a cubic --nsub and one GPU")
+        return problem.poisson_q1_cube(a.ncell, (p, p, p), overlap=a.overlap, coarse=a.coarse, nev=a.nev, **kw)
     g = gpu_grid(world)
     shape = tuple(a.ncell * k for k in g)
     coords, cells = mesh.structured_simplices(shape, lengths=tuple(float(k) for k in g))
@@ -311,7 +323,7 @@ def run_b200(a):
     traffic = None
     try:
         tr = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))
-        traffic = tr.get(f"ncell{a.ncell}_nsub{a.nsub}_{a.coarse}_nev{a.nev}_overlap{a.overlap}", {}).get(f"{dom}_kernel")
+        traffic = tr.get(f"{'' if a.workload == 'p1cube' else a.workload + '_'}ncell{a.ncell}_nsub{a.nsub}_{a.coarse}_nev{a.nev}_overlap{a.overlap}", {}).get(f"{dom}_kernel")
     except OSError:
         pass
     line = {

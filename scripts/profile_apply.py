@@ -25,6 +25,7 @@ ctypes.CDLL("libcuda.so.1").cuProfilerStart()  # ncu --profile-from-start off: s
 ctx.timers(True)
 for _ in range(napply):
     C.apply(x, d)
+    op.apply(d, x)
 ctx.sync()
 for ev in ("Schwarz/local solve fwd", "Schwarz/local solve bwd", "CombinedPreconditioner/apply"):
     ms, n = ctx.timer(ev)
