@@ -126,6 +126,8 @@ struct ddm_ctx {
     int device = 0;
     int sm_count = 148;
     cudaStream_t s = nullptr;
+    cudaStream_t s2 = nullptr;  // side stream: the coarse solve runs beside the triangular sweeps (additive mode)
+    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     int64_t launches = 0;
     // operator
     int64_t n_own = 0, n_ghost = 0, nloc = 0, nnz = 0;
@@ -193,11 +195,12 @@ struct ddm_vec {
     double *d;
 };
 
-#define LAUNCH(ctx, kern, grid, block, ...)                       \
+#define LAUNCH_ON(ctx, st, kern, grid, block, ...)                \
     do {                                                          \
-        kern<<<(grid), (block), 0, (ctx)->s>>>(__VA_ARGS__);      \
+        kern<<<(grid), (block), 0, (st)>>>(__VA_ARGS__);          \
         (ctx)->launches++;                                        \
     } while (0)
+#define LAUNCH(ctx, kern, grid, block, ...) LAUNCH_ON(ctx, (ctx)->s, kern, grid, block, __VA_ARGS__)
 
 static inline int nblocks(int64_t n, int per = 256) { return (int)std::max<int64_t>(1, (n + per - 1) / per); }
 static inline int stream_grid(ddm_ctx *c, int64_t n)
@@ -207,21 +210,22 @@ static inline int stream_grid(ddm_ctx *c, int64_t n)
 
 struct ScopedTimer {
     ddm_ctx *c;
+    cudaStream_t st;
     size_t idx = (size_t)-1;
-    ScopedTimer(ddm_ctx *c_, const char *name) : c(c_)
+    ScopedTimer(ddm_ctx *c_, const char *name, cudaStream_t st_ = nullptr) : c(c_), st(st_ ? st_ : c_->s)
     {
         if (!c->timers_on) return;
         TimerRec r;
         r.name = name;
         cudaEventCreate(&r.a);
         cudaEventCreate(&r.b);
-        cudaEventRecord(r.a, c->s);
+        cudaEventRecord(r.a, st);
         c->trecs.push_back(r);
         idx = c->trecs.size() - 1;
     }
     ~ScopedTimer()
     {
-        if (idx != (size_t)-1) cudaEventRecord(c->trecs[idx].b, c->s);
+        if (idx != (size_t)-1) cudaEventRecord(c->trecs[idx].b, st);
     }
 };
 
@@ -247,6 +251,9 @@ extern "C" int ddm_ctx_create(int device, ddm_ctx **out)
     CU(cudaGetDeviceProperties(&prop, device));
     c->sm_count = prop.multiProcessorCount;
     CU(cudaStreamCreateWithFlags(&c->s, cudaStreamNonBlocking));
+    CU(cudaStreamCreateWithFlags(&c->s2, cudaStreamNonBlocking));
+    CU(cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming));
+    CU(cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming));
     c->nred = c->sm_count * 4;
     CU(cudaMalloc((void **)&c->partial, sizeof(double) * c->nred));
     CU(cudaMalloc((void **)&c->scal, sizeof(double) * 16));
@@ -295,6 +302,9 @@ extern "C" int ddm_ctx_destroy(ddm_ctx *c)
         cudaEventDestroy(c->sw1);
     }
     cudaStreamDestroy(c->s);
+    cudaStreamDestroy(c->s2);
+    cudaEventDestroy(c->ev_fork);
+    cudaEventDestroy(c->ev_join);
     delete c;
     return 0;
 }
@@ -407,7 +417,9 @@ extern "C" int ddm_upload_operator(ddm_ctx *c, int64_t n_own, int64_t n_ghost, c
     CK(dev_upload(&c->col, col, (size_t)nnz));
     CK(dev_upload(&c->val, val, (size_t)nnz));
     const double mean = n_own ? (double)nnz / (double)n_own : 1.0;
-    c->spmv_group = mean <= 3 ? 2 : mean <= 6 ? 4 : mean <= 40 ? 8 : mean <= 96 ? 16 : 32;
+    // lanes per row: measured on B200 at 15 nnz/row (3-D P1): G=4 60 us, G=8 91 us, G=16 149 us for 21.6 M nonzeros --
+    // short dependent chains per lane beat idle lanes, so a lane takes about four entries of its row
+    c->spmv_group = mean <= 6 ? 2 : mean <= 24 ? 4 : mean <= 48 ? 8 : mean <= 128 ? 16 : 32;
     if (const char *e = getenv("DDM_SPMV_GROUP")) c->spmv_group = atoi(e);
     c->stats["spmv"] = 12.0 * nnz + 4.0 * (n_own + 1) + 16.0 * n_own;
     c->stats["dot"] = 16.0 * n_own;
@@ -1215,18 +1227,19 @@ static int restrict_all(ddm_ctx *c, const double *d, int with_coarse)
     return 0;
 }
 
-static int coarse_solve(ddm_ctx *c)
+static int coarse_solve(ddm_ctx *c, cudaStream_t st = nullptr)
 {
-    ScopedTimer tm(c, "GalerkinPrec/coarse solve");
+    if (!st) st = c->s;
+    ScopedTimer tm(c, "GalerkinPrec/coarse solve", st);
     const int N0 = c->N0;
-    if (c->nranks > 1) CU(cudaMemsetAsync(c->d0, 0, sizeof(double) * N0, c->s));
-    LAUNCH(c, coarse_restrict_final_kernel, c->nsub, 64, c->nsub, c->seg_ptr, c->d_sub_k, c->d_koff, c->cpartial, c->kpad, c->d0);
-    if (c->nranks > 1) NC(g_nccl.AllReduce(c->d0, c->d0, N0, ncclDouble, ncclSum, c->comm, c->s)); // gatherv (galerkin_preconditioner.hh:171)
+    if (c->nranks > 1) CU(cudaMemsetAsync(c->d0, 0, sizeof(double) * N0, st));
+    LAUNCH_ON(c, st, coarse_restrict_final_kernel, c->nsub, 64, c->nsub, c->seg_ptr, c->d_sub_k, c->d_koff, c->cpartial, c->kpad, c->d0);
+    if (c->nranks > 1) NC(g_nccl.AllReduce(c->d0, c->d0, N0, ncclDouble, ncclSum, c->comm, st)); // gatherv (galerkin_preconditioner.hh:171)
     const int grid = nblocks((int64_t)N0 * 32);
     // y = A0inv d0, then one refinement step: y += A0inv (d0 - A0 y)
-    LAUNCH(c, dense_gemv_kernel, grid, 256, N0, c->A0inv, c->d0, c->y0, (const double *)nullptr, 1.0);
-    LAUNCH(c, dense_gemv_kernel, grid, 256, N0, c->A0, c->y0, c->r0, c->d0, -1.0);
-    LAUNCH(c, dense_gemv_kernel, grid, 256, N0, c->A0inv, c->r0, c->y0, c->y0, 1.0);
+    LAUNCH_ON(c, st, dense_gemv_kernel, grid, 256, N0, c->A0inv, c->d0, c->y0, (const double *)nullptr, 1.0);
+    LAUNCH_ON(c, st, dense_gemv_kernel, grid, 256, N0, c->A0, c->y0, c->r0, c->d0, -1.0);
+    LAUNCH_ON(c, st, dense_gemv_kernel, grid, 256, N0, c->A0inv, c->r0, c->y0, c->y0, 1.0);
     return 0;
 }
 
@@ -1308,9 +1321,18 @@ extern "C" int ddm_twolevel_apply(ddm_ctx *c, int type, int mode, int with_coars
     }
     if (mode == DDM_COMBINE_ADDITIVE) {
         // one restriction and one prolongation serve both levels (the reference does each twice)
+        // the coarse solve (a few latency-bound launches) runs on the side stream beside the sweeps
         CK(restrict_all(c, d->d, 1));
-        CK(coarse_solve(c));
+        const bool side = getenv("DDM_NO_SIDE_STREAM") == nullptr;
+        if (side) {
+            CU(cudaEventRecord(c->ev_fork, c->s));
+            CU(cudaStreamWaitEvent(c->s2, c->ev_fork, 0));
+            CK(coarse_solve(c, c->s2));
+            CU(cudaEventRecord(c->ev_join, c->s2));
+        } else
+            CK(coarse_solve(c));
         CK(trisolve(c));
+        if (side) CU(cudaStreamWaitEvent(c->s, c->ev_join, 0));
         return prolong(c, x->d, 1, restricted, 1, 0);
     }
     // multiplicative: x = M1 d;  x += M0 (d - A x)   (combined_preconditioner.hh:144-158)

@@ -239,9 +239,13 @@ __global__ void __launch_bounds__(256) restrict_kernel(const Segment *__restrict
                 W[p] = v;
                 if (W2) W2[p] = 0.0;
             }
+            // all basis loads of this position are issued before the first use (the compiler otherwise pairs each load
+            // with its FMA and keeps two in flight)
+            double z[kKmax];
 #pragma unroll
-            for (int j = 0; j < kKmax; ++j)
-                if (k0 + j < k) acc[j] = fma(Zi[(int64_t)(k0 + j) * ni + t], v, acc[j]);
+            for (int j = 0; j < kKmax; ++j) z[j] = (k0 + j < k) ? __ldcs(Zi + (int64_t)(k0 + j) * ni + t) : 0.0;
+#pragma unroll
+            for (int j = 0; j < kKmax; ++j) acc[j] = fma(z[j], v, acc[j]);
         }
         if (k > 0) {
 #pragma unroll

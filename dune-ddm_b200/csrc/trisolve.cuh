@@ -98,7 +98,9 @@ __device__ __forceinline__ void wait_counter(const int *cnt, int need, int lane)
     if (need > 0) {
         if (lane == 0) {
             while (ld_relaxed(cnt) < need) __nanosleep(20);
+#ifndef DDM_RELAXED_WAIT
             (void)ld_acquire(cnt);
+#endif
         }
         __syncwarp();
     }

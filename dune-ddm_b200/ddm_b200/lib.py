@@ -6,7 +6,7 @@ import os
 import subprocess
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(os.path.dirname(_HERE), "libddm_b200.so")
+LIB_PATH = os.environ.get("DDM_B200_LIB") or os.path.join(os.path.dirname(_HERE), "libddm_b200.so")  # override: kernel experiments
 BUILD_SH = os.path.join(os.path.dirname(_HERE), "csrc", "build.sh")
 
 SYMBOLS = [

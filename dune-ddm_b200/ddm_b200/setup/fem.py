@@ -101,6 +101,20 @@ def assemble(n, cells, Ke, subset=None):
     return A
 
 
+def assemble_chunked(n, cells, ke_fn, chunk=4_000_000):
+    """assemble() over chunks of cells, element matrices produced on the fly by ke_fn(index array): bounds the transient
+    memory of large meshes (several ranks build the same global matrix side by side)."""
+    A = None
+    for lo in range(0, cells.shape[0], chunk):
+        idx = np.arange(lo, min(lo + chunk, cells.shape[0]))
+        part = assemble(n, cells[idx], ke_fn(idx))
+        A = part if A is None else A + part
+    A = A.tocsr()
+    A.sum_duplicates()
+    A.sort_indices()
+    return A
+
+
 def eliminate_dirichlet(A, dirichlet):
     """Identity rows / zero columns at constrained DOFs; pattern is kept.
 

@@ -110,11 +110,12 @@ def _sub_job(i):
 
 def build(coords, cells, Ke, dirichlet, rhs, cell_part, nsub, overlap=2, pou_kind="distance", shrink=0,
           coarse="geneo", nev=16, shift=1e-3, eig_tol=1e-5, leaf_size=32, workers=None, meta=None, only=None, gather=None,
-          A_full=None, symmetric=True):
+          A_full=None, symmetric=True, ke_fn=None):
     """Generic pipeline from an element-wise description to SetupProducts.
 
     only / gather: with several processes (one per GPU) every process factors and builds the coarse basis of its own
-    subdomains `only` (the reference does the same: one rank, one subdomain) and `gather(obj) -> [obj of rank 0, ...]`
+    subdomains `only` (the reference does the same: one rank, one subdomain; with ke_fn(cell ids) -> element matrices
+    given instead of Ke, element matrices are kept only for the cells that touch those subdomains) and `gather(obj) -> [obj of rank 0, ...]`
     exchanges the bases and the column blocks of the Galerkin matrix (the reference's neighbour exchange and
     gatherMatrixFromRows, galerkin_preconditioner.hh:246-328).  Factors of other ranks' subdomains stay None."""
     import time
@@ -142,10 +143,17 @@ def build(coords, cells, Ke, dirichlet, rhs, cell_part, nsub, overlap=2, pou_kin
     shared = np.zeros(n, dtype=np.int32)
     for s in subs:
         shared[s] += 1
+    todo = list(range(nsub)) if only is None else list(only)
+    if Ke is None and ke_fn is not None and coarse == "geneo":
+        # element matrices for the Neumann problems of the subdomains this process handles
+        mine = np.zeros(n, dtype=bool)
+        for i in todo:
+            mine[subs[i]] = True
+        keep = np.flatnonzero(mine[cells].all(axis=1))
+        cells, Ke = cells[keep], ke_fn(keep)
     _G.clear()
     _G.update(A=A, subs=subs, coords=coords, cells=cells, Ke=Ke, dirichlet=dirichlet, shared=shared, pou=pou,
               coarse=coarse, nev=nev, shift=shift, eig_tol=eig_tol, leaf_size=leaf_size, symmetric=symmetric)
-    todo = list(range(nsub)) if only is None else list(only)
     workers = workers or min(max(len(todo), 1), os.cpu_count() or 1)
     factors = [None] * nsub
     Z = [None] * nsub
@@ -178,15 +186,20 @@ def poisson_simplex(coords, cells, nsub, kappa_fn=fem.kappa_islands, xmax=1.0, *
     """P1 Poisson with Dirichlet data g = 1 - x/xmax on x in {0, xmax} (poisson_coefficient.lua:1-3,38-44)."""
     d = coords.shape[1]
     cent = coords[cells].mean(axis=1)
-    Ke = fem.p1_element_matrices(coords, cells, kappa_fn(cent))
+    kap = kappa_fn(cent)
+
+    def ke_fn(idx):
+        return fem.p1_element_matrices(coords, cells[idx], kap[idx])
+
     dirichlet = (coords[:, 0] < 1e-6) | (coords[:, 0] > xmax - 1e-6)
     n = coords.shape[0]
+    A_full = fem.assemble_chunked(n, cells, ke_fn)  # element matrices are produced chunk by chunk, never all at once
     # residual at the Dirichlet lift x0 (g on the boundary, 0 inside): d = A_full x0 - f, f = 0
     x0 = np.where(dirichlet, 1.0 - coords[:, 0] / xmax, 0.0)
-    rhs = fem.assemble(n, cells, Ke) @ x0
+    rhs = A_full @ x0
     part = decomp.rcb_partition(cent, nsub)
     meta = dict(kw.pop("meta", {}), problem="poisson-p1", dim=d)
-    return build(coords, cells, Ke, dirichlet, rhs, part, nsub, meta=meta, **kw)
+    return build(coords, cells, None, dirichlet, rhs, part, nsub, meta=meta, A_full=A_full, ke_fn=ke_fn, **kw)
 
 
 def poisson_q1_cube(ncell, pgrid, kappa_fn=fem.kappa_channels, **kw):
