@@ -78,7 +78,7 @@ def build_problem(a, world, rank=None, gather=None):
         from ddm_b200.partition import sub_ranges
 
         s0, s1 = sub_ranges(a.nsub * world, world)[rank]
-        kw = dict(only=range(s0, s1), gather=gather, workers=max(1, (os.cpu_count() or 1) // world))
+        kw = dict(only=range(s0, s1), gather=gather, workers=max(1, (os.cpu_count() or 1) // world), assemble_part=(rank, world))
     P = _build_problem(a, world, fem, mesh, problem, **kw)
     if a.pack and gather is None:
         pack.save_products(a.pack, P)

@@ -147,6 +147,7 @@ struct ddm_ctx {
     std::vector<int32_t> sub_k, koff;
     std::vector<double> Z_host;
     int32_t N0 = 0, k_offset = 0, kpad = 0;
+    bool A0_pending = false;  // coarse basis uploaded without a Galerkin matrix
     double *A0 = nullptr, *A0inv = nullptr, *d0 = nullptr, *y0 = nullptr, *r0 = nullptr;
     // finalized device schedules
     bool finalized = false;
@@ -731,22 +732,11 @@ extern "C" int ddm_upload_factor_lu(ddm_ctx *c, int32_t sub, int32_t n, int32_t 
     return upload_factor_impl(c, sub, n, nsuper, super, pi, px, s, xl, xu, perm);
 }
 
-extern "C" int ddm_upload_coarse(ddm_ctx *c, const int32_t *k, const double *Z, int32_t N0, int32_t k_offset, const double *A0)
+// A0 (device, row-major, c->A0) -> explicit inverse c->A0inv; A0 points to a host copy (symmetry test).
+static int coarse_factor(ddm_ctx *c, const double *A0)
 {
-    CU(cudaSetDevice(c->device));
-    if (!c->nsub) return fail("upload the decomposition before the coarse space");
-    c->sub_k.assign(k, k + c->nsub);
-    int64_t tot = 0;
-    for (int32_t i = 0; i < c->nsub; ++i) tot += (int64_t)k[i] * (c->sub_ptr[i + 1] - c->sub_ptr[i]);
-    c->Z_host.assign(Z, Z + tot);
-    c->N0 = N0;
-    c->k_offset = k_offset;
-    if (N0 <= 0) return 0;
-    CK(dev_upload(&c->A0, A0, (size_t)N0 * N0));
-    CK(dev_upload(&c->A0inv, A0, (size_t)N0 * N0));
-    CU(cudaMalloc((void **)&c->d0, sizeof(double) * N0));
-    CU(cudaMalloc((void **)&c->y0, sizeof(double) * N0));
-    CU(cudaMalloc((void **)&c->r0, sizeof(double) * N0));
+    const int32_t N0 = c->N0;
+    CU(cudaMemcpyAsync(c->A0inv, c->A0, sizeof(double) * (size_t)N0 * N0, cudaMemcpyDeviceToDevice, c->s));
     // A0^{-1} by dense Cholesky (setup, once; the reference factors A0 with a sparse direct solver on rank 0,
     // galerkin_preconditioner.hh:331-346).
     cusolverDnHandle_t h;
@@ -789,7 +779,6 @@ extern "C" int ddm_upload_coarse(ddm_ctx *c, const int32_t *k, const double *Z, 
         cudaFree(info);
         cudaFree(ipiv);
         cusolverDnDestroy(h);
-        c->finalized = false;
         return 0;
     }
     int lwork = 0, lwork2 = 0;
@@ -820,6 +809,34 @@ extern "C" int ddm_upload_coarse(ddm_ctx *c, const int32_t *k, const double *Z, 
             M[(size_t)i * N0 + j] = M[(size_t)j * N0 + i];
         }
     CU(cudaMemcpy(c->A0inv, M.data(), sizeof(double) * M.size(), cudaMemcpyHostToDevice));
+    return 0;
+}
+
+extern "C" int ddm_upload_coarse(ddm_ctx *c, const int32_t *k, const double *Z, int32_t N0, int32_t k_offset, const double *A0)
+{
+    CU(cudaSetDevice(c->device));
+    if (!c->nsub) return fail("upload the decomposition before the coarse space");
+    c->sub_k.assign(k, k + c->nsub);
+    int64_t tot = 0;
+    for (int32_t i = 0; i < c->nsub; ++i) tot += (int64_t)k[i] * (c->sub_ptr[i + 1] - c->sub_ptr[i]);
+    c->Z_host.assign(Z, Z + tot);
+    c->N0 = N0;
+    c->k_offset = k_offset;
+    if (N0 <= 0) return 0;
+    for (double **p : {&c->A0, &c->A0inv, &c->d0, &c->y0, &c->r0}) {
+        cudaFree(*p);
+        *p = nullptr;
+    }
+    CU(cudaMalloc((void **)&c->A0, sizeof(double) * (size_t)N0 * N0));
+    CU(cudaMalloc((void **)&c->A0inv, sizeof(double) * (size_t)N0 * N0));
+    CU(cudaMalloc((void **)&c->d0, sizeof(double) * N0));
+    CU(cudaMalloc((void **)&c->y0, sizeof(double) * N0));
+    CU(cudaMalloc((void **)&c->r0, sizeof(double) * N0));
+    c->A0_pending = A0 == nullptr;  // NULL: the Galerkin matrix is assembled on the device (ddm_galerkin_assemble)
+    if (A0) {
+        CU(cudaMemcpy(c->A0, A0, sizeof(double) * (size_t)N0 * N0, cudaMemcpyHostToDevice));
+        CK(coarse_factor(c, A0));
+    }
     c->finalized = false;
     return 0;
 }
@@ -993,6 +1010,14 @@ extern "C" int ddm_finalize(ddm_ctx *c)
         return a.level != b.level ? a.level < b.level : da < db;
     });
     std::stable_sort(bkeys.begin(), bkeys.end(), [](const Key &a, const Key &b) { return a.level > b.level; });
+    if (const char *e = getenv("DDM_FWD_SKIP")) {  // timing experiments only (results are wrong): drop one class of forward tasks
+        const bool drop_diag = strcmp(e, "diag") == 0;
+        std::vector<Key> kept;
+        for (const Key &k : fkeys)
+            if (((k.kind & 1) != 0) != drop_diag) kept.push_back(k);
+        fkeys.swap(kept);
+        if (!drop_diag) std::fill(need.begin(), need.end(), 0);
+    }
     std::vector<TriTask> fwd, bwd;
     fwd.reserve(fkeys.size());
     bwd.reserve(bkeys.size());
@@ -1300,6 +1325,7 @@ extern "C" int ddm_coarse_apply(ddm_ctx *c, ddm_vec *d, ddm_vec *x)
 {
     CK(need_final(c));
     if (c->N0 <= 0) return fail("no coarse space uploaded");
+    if (c->A0_pending) return fail("the coarse basis was uploaded without a Galerkin matrix: call ddm_galerkin_assemble");
     ScopedTimer tm(c, "GalerkinPrec/apply");
     CK(halo_forward(c, d->d));
     CK(restrict_all(c, d->d, 1));
@@ -1311,6 +1337,7 @@ extern "C" int ddm_twolevel_apply(ddm_ctx *c, int type, int mode, int with_coars
 {
     CK(need_final(c));
     if (with_coarse && c->N0 <= 0) return fail("no coarse space uploaded");
+    if (with_coarse && c->A0_pending) return fail("the coarse basis was uploaded without a Galerkin matrix: call ddm_galerkin_assemble");
     ScopedTimer tm(c, "CombinedPreconditioner/apply");
     const int restricted = type == DDM_SCHWARZ_RESTRICTED;
     CK(halo_forward(c, d->d));
@@ -1346,6 +1373,37 @@ extern "C" int ddm_twolevel_apply(ddm_ctx *c, int type, int mode, int with_coars
     CK(restrict_all(c, dn, 1));
     CK(coarse_solve(c));
     return prolong(c, x->d, 0, 0, 1, 1);
+}
+
+// N1: the Galerkin product A0 = Z^T A Z on the device, column by column with the solve-phase kernels:
+//   column j = restrict_coarse( A * prolong_coarse(e_j) )
+// (GalerkinPreconditioner::build_solver computes the same entries from A Z_i and neighbour exchanges,
+// dune/ddm/galerkin_preconditioner.hh:246-328).  Works across ranks (halo exchange + all-reduce of each column).
+extern "C" int ddm_galerkin_assemble(ddm_ctx *c, double *A0_out)
+{
+    CK(need_final(c));
+    const int32_t N0 = c->N0;
+    if (N0 <= 0) return fail("no coarse space uploaded");
+    double *x = c->tmp[0]->d, *y = c->tmp[1]->d;
+    for (int32_t j = 0; j < N0; ++j) {
+        CU(cudaMemsetAsync(c->y0, 0, sizeof(double) * N0, c->s));
+        LAUNCH(c, fill_kernel, 1, 32, 1, 1.0, c->y0 + j);
+        CK(prolong(c, x, 0, 0, 1, 0));
+        CK(spmv(c, x, y, 1.0, 0));
+        CK(halo_forward(c, y));
+        CK(restrict_all(c, y, 1));
+        if (c->nranks > 1) CU(cudaMemsetAsync(c->d0, 0, sizeof(double) * N0, c->s));
+        LAUNCH(c, coarse_restrict_final_kernel, c->nsub, 64, c->nsub, c->seg_ptr, c->d_sub_k, c->d_koff, c->cpartial, c->kpad, c->d0);
+        if (c->nranks > 1) NC(g_nccl.AllReduce(c->d0, c->d0, N0, ncclDouble, ncclSum, c->comm, c->s));
+        CU(cudaMemcpy2DAsync(c->A0 + j, sizeof(double) * N0, c->d0, sizeof(double), sizeof(double), N0, cudaMemcpyDeviceToDevice, c->s));
+    }
+    std::vector<double> A0((size_t)N0 * N0);
+    CU(cudaMemcpyAsync(A0.data(), c->A0, sizeof(double) * A0.size(), cudaMemcpyDeviceToHost, c->s));
+    CU(cudaStreamSynchronize(c->s));
+    CK(coarse_factor(c, A0.data()));
+    c->A0_pending = false;
+    if (A0_out) memcpy(A0_out, A0.data(), sizeof(double) * A0.size());
+    return 0;
 }
 
 // ------------------------------------------------------------------------------------------------ PCG

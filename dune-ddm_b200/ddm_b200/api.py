@@ -88,8 +88,9 @@ class Context:
         self.world = 1
 
     @classmethod
-    def from_products(cls, P, device=0, rank=0, world=1, unique_id=None, with_coarse=True):
-        """Upload the setup products (whole problem, or this rank's shard)."""
+    def from_products(cls, P, device=0, rank=0, world=1, unique_id=None, with_coarse=True, device_galerkin=False):
+        """Upload the setup products (whole problem, or this rank's shard).  device_galerkin: do not upload P.A0 but
+        assemble Z^T A Z on the GPU (ddm_galerkin_assemble); the result is kept in self.A0_device."""
         self = cls(device)
         S = shard(P, rank, world)
         self.shard, self.world, self.rank = S, world, rank
@@ -144,8 +145,11 @@ class Context:
             Z = np.concatenate([P.Z[i].ravel(order="F") for i in range(a, b)]) if b > a else np.zeros(1)
             A0 = np.ascontiguousarray(P.A0, dtype=np.float64)
             check(lib.ddm_upload_coarse(self.h, _p(k, C.c_int32), _p(np.ascontiguousarray(Z), C.c_double), C.c_int32(N0),
-                                        C.c_int32(S.k_offset), _p(A0, C.c_double)))
+                                        C.c_int32(S.k_offset), None if device_galerkin else _p(A0, C.c_double)))
         check(lib.ddm_finalize(self.h))
+        if with_coarse and N0 > 0 and device_galerkin:
+            self.A0_device = np.empty((N0, N0))
+            check(lib.ddm_galerkin_assemble(self.h, _p(self.A0_device, C.c_double)))
         return self
 
     # -- helpers

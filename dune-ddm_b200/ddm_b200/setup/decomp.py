@@ -130,16 +130,12 @@ def graph_distance(Ai, seeds, maxdist):
     return dist
 
 
-def partition_of_unity(A, subs, bmasks, owner, kind="distance", shrink=0, overlap=1):
-    """Partition-of-unity weights D_i per overlapping subdomain (pou.hh:79-140).
-
-    The reference computes the distance with 4*overlap+1 Gauss-Seidel sweeps; every value
-    <= 4*overlap it can produce equals the true graph distance, and larger values all map
-    to weight 1, so a breadth-first search gives identical weights.
-    """
-    n = A.shape[0]
-    raw = []
-    for r, (s, bm) in enumerate(zip(subs, bmasks)):
+def pou_raw(A, subs, bmasks, owner, kind="distance", shrink=0, overlap=1, ids=None):
+    """Un-normalised weights of the subdomains `ids` (default: all), pou.hh:79-127."""
+    ids = range(len(subs)) if ids is None else ids
+    raw = {}
+    for r in ids:
+        s, bm = subs[r], bmasks[r]
         if kind == "trivial":
             w = (owner[s] == r).astype(np.float64)
         elif kind == "standard":
@@ -152,9 +148,14 @@ def partition_of_unity(A, subs, bmasks, owner, kind="distance", shrink=0, overla
             w[near] = np.maximum(dist[near] - shrink, 0).astype(np.float64)
         else:
             raise ValueError(f"unknown partition of unity type {kind!r}")
-        raw.append(w)
+        raw[r] = w
+    return raw
+
+
+def pou_normalise(n, subs, raw, bmasks, kind="distance"):
+    """Divide by the sum over all subdomains that see a DOF (the halo sum of pou.hh:128-140)."""
     if kind == "trivial":
-        return raw
+        return list(raw)
     total = np.zeros(n)
     for s, w in zip(subs, raw):
         np.add.at(total, s, w)
@@ -164,3 +165,14 @@ def partition_of_unity(A, subs, bmasks, owner, kind="distance", shrink=0, overla
             d = np.where(bm, 0.0, w / total[s])
         pou.append(d)
     return pou
+
+
+def partition_of_unity(A, subs, bmasks, owner, kind="distance", shrink=0, overlap=1):
+    """Partition-of-unity weights D_i per overlapping subdomain (pou.hh:79-140).
+
+    The reference computes the distance with 4*overlap+1 Gauss-Seidel sweeps; every value
+    <= 4*overlap it can produce equals the true graph distance, and larger values all map
+    to weight 1, so a breadth-first search gives identical weights.
+    """
+    raw = pou_raw(A, subs, bmasks, owner, kind, shrink, overlap)
+    return pou_normalise(A.shape[0], subs, [raw[r] for r in range(len(subs))], bmasks, kind)

@@ -135,15 +135,27 @@ def build(coords, cells, Ke, dirichlet, rhs, cell_part, nsub, overlap=2, pou_kin
     b = np.where(dirichlet, 0.0, rhs)
     tick("assemble")
     novlp, owner = decomp.nonoverlapping_sets(n, cells, cell_part, nsub)
-    subs = decomp.grow_overlap(A_full, novlp, overlap)
+    todo = list(range(nsub)) if only is None else list(only)
+
+    def everyone(local):  # {subdomain: value} of this process -> list over all subdomains
+        if gather is None:
+            return [local[i] for i in range(nsub)]
+        full = [None] * nsub
+        for part in gather(local):
+            for i, v in part.items():
+                full[i] = v
+        return full
+
+    # overlap growth, boundary masks and raw partition-of-unity weights are per-subdomain work: each process does its own
+    subs = everyone(dict(zip(todo, decomp.grow_overlap(A_full, [novlp[i] for i in todo], overlap))))
     tick("overlap")
-    bmasks = decomp.boundary_masks(A_full, subs)
-    pou = decomp.partition_of_unity(A_full, subs, bmasks, owner, pou_kind, shrink, overlap)
+    bmasks = everyone(dict(zip(todo, decomp.boundary_masks(A_full, [subs[i] for i in todo]))))
+    raw = everyone(decomp.pou_raw(A_full, subs, bmasks, owner, pou_kind, shrink, overlap, ids=todo))
+    pou = decomp.pou_normalise(n, subs, raw, bmasks, pou_kind)
     tick("pou")
     shared = np.zeros(n, dtype=np.int32)
     for s in subs:
         shared[s] += 1
-    todo = list(range(nsub)) if only is None else list(only)
     if Ke is None and ke_fn is not None and coarse == "geneo":
         # element matrices for the Neumann problems of the subdomains this process handles
         mine = np.zeros(n, dtype=bool)
@@ -193,7 +205,20 @@ def poisson_simplex(coords, cells, nsub, kappa_fn=fem.kappa_islands, xmax=1.0, *
 
     dirichlet = (coords[:, 0] < 1e-6) | (coords[:, 0] > xmax - 1e-6)
     n = coords.shape[0]
-    A_full = fem.assemble_chunked(n, cells, ke_fn)  # element matrices are produced chunk by chunk, never all at once
+    part_of = kw.pop("assemble_part", None)
+    if part_of is not None and kw.get("gather") is not None:
+        # several processes: each assembles its slice of the cells, the partial matrices are exchanged and summed in rank order
+        r, w = part_of
+        lo, hi = cells.shape[0] * r // w, cells.shape[0] * (r + 1) // w
+        A_loc = fem.assemble_chunked(n, cells[lo:hi], lambda idx: ke_fn(idx + lo))
+        A_full = None
+        for ip, ix, da in kw["gather"]((A_loc.indptr, A_loc.indices, A_loc.data)):
+            Ap = sp.csr_matrix((da, ix, ip), shape=(n, n))
+            A_full = Ap if A_full is None else A_full + Ap
+        A_full.sum_duplicates()
+        A_full.sort_indices()
+    else:
+        A_full = fem.assemble_chunked(n, cells, ke_fn)  # element matrices are produced chunk by chunk, never all at once
     # residual at the Dirichlet lift x0 (g on the boundary, 0 inside): d = A_full x0 - f, f = 0
     x0 = np.where(dirichlet, 1.0 - coords[:, 0] / xmax, 0.0)
     rhs = A_full @ x0

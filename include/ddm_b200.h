@@ -115,6 +115,12 @@ int ddm_upload_coarse(ddm_ctx *ctx, const int32_t *k, const double *Z, int32_t N
 /* Builds the device schedules; call after all uploads. */
 int ddm_finalize(ddm_ctx *ctx);
 
+/* Galerkin product A0 = Z^T A Z on the device (GalerkinPreconditioner::build_solver, dune/ddm/galerkin_preconditioner.hh:246-328,
+ * which the reference flags as a bottleneck for large runs, :217-218): call after ddm_finalize when ddm_upload_coarse was given
+ * A0 = NULL.  Every column is restrict(A * prolong(e_j)) with the solve-phase kernels, all-reduced over the ranks; the matrix
+ * is then factored like an uploaded one.  A0_out (N0 x N0 row-major, may be NULL) receives a copy. */
+int ddm_galerkin_assemble(ddm_ctx *ctx, double *A0_out);
+
 /* ---- vectors: the operations Dune's Krylov solvers need from X --------------------------
  * (extern/dune-istl/dune/istl/solvers.hh:292-335,933-1012: copy, =scalar, =X, axpy, *=, +=) */
 int ddm_vec_create(ddm_ctx *ctx, ddm_vec **out);
