@@ -299,6 +299,14 @@ def run_b200(a):
         dist.all_reduce(vals, op=dist.ReduceOp.MAX)
     dev_ms, t_wall, t_e2e = vals.tolist()
     stats = {k: ctx.stat(k) for k in ("trisolve_fwd", "trisolve_bwd", "trisolve_stored", "spmv", "restrict", "prolong", "coarse", "factor_nnz")}
+    per_rank = [None] * world  # load balance of the sharded path: factor entries and sweep times per rank
+    fwd_ms, fwd_calls = timers["Schwarz/local solve fwd"]
+    bwd_ms, bwd_calls = timers["Schwarz/local solve bwd"]
+    mine = {"factor_nnz": stats["factor_nnz"], "fwd_ms": fwd_ms / max(fwd_calls, 1), "bwd_ms": bwd_ms / max(bwd_calls, 1), "dofs_owned": int(ctx.n_own)}
+    if world > 1:
+        dist.all_gather_object(per_rank, mine)
+    else:
+        per_rank = [mine]
     if rank != 0:
         if world > 1:
             dist.barrier()
@@ -343,6 +351,7 @@ def run_b200(a):
                      "algorithmic_bytes_per_launch": stats[dom], "ms_per_launch": kern[dom]["ms"], "kernels": kern},
         "timers_ms_per_call": {k: (v[0] / max(v[1], 1)) for k, v in timers.items()},
         "clocks": clk.summary(),
+        "per_rank": per_rank,
     }
     if not a.no_cpu_baseline:
         from oracle import oracle

@@ -111,6 +111,7 @@ struct SubFactor {
     double *panelU = nullptr;       // LU factors: tiles of -Ut^T (below rows only), read by the backward sweep
     std::vector<int64_t> ubelow_off;
     bool lu = false;
+    uint64_t sig = 0;               // hash of the symbolic structure (super, pi, s, perm): equal => value update in place
     int32_t *rowidx = nullptr;      // device: absolute WX offsets, filled at finalize
     std::vector<int32_t> rows_host; // -1 padding, -2-k = X position k (diagonal rows), >= 0 W position (below rows)
     int64_t panel_doubles = 0, nnz_lower = 0;
@@ -458,6 +459,15 @@ extern "C" int ddm_upload_operator_bcsr3(ddm_ctx *c, int64_t nb_own, int64_t nb_
     return 0;
 }
 
+extern "C" int ddm_update_operator_values(ddm_ctx *c, const double *val)
+{
+    CU(cudaSetDevice(c->device));
+    if (!c->rowptr) return fail("no operator uploaded");
+    CU(cudaMemcpyAsync(c->val, val, sizeof(double) * (size_t)c->nnz, cudaMemcpyHostToDevice, c->s));
+    CU(cudaStreamSynchronize(c->s));
+    return 0;
+}
+
 extern "C" int ddm_upload_decomposition(ddm_ctx *c, int32_t nsub, const int64_t *sub_ptr, const int32_t *sub_dofs,
                                         const double *pou)
 {
@@ -513,7 +523,31 @@ static int upload_factor_impl(ddm_ctx *c, int32_t sub, int32_t n, int32_t nsuper
     if (sub < 0 || sub >= c->nsub) return fail("factor for subdomain %d, but %d are hosted", sub, c->nsub);
     if (n != c->sub_ptr[sub + 1] - c->sub_ptr[sub]) return fail("factor size %d != subdomain size %lld", n, (long long)(c->sub_ptr[sub + 1] - c->sub_ptr[sub]));
     SubFactor &F = c->fac[sub];
+    // Same symbolic structure as the factor already uploaded (a Newton step, TwoLevelSchwarzSolver::apply's update branch,
+    // dune/ddm/twolevel_schwarz.hh:99-104): convert the new values into the existing tile arrays, schedules stay valid.
+    uint64_t sig = 1469598103934665603ull;
+    auto mix = [&](const void *p, size_t bytes) {
+        const unsigned char *b = static_cast<const unsigned char *>(p);
+        for (size_t q = 0; q < bytes; ++q) sig = (sig ^ b[q]) * 1099511628211ull;
+    };
+    mix(&n, sizeof n);
+    mix(super, sizeof(int32_t) * (nsuper + 1));
+    mix(pi, sizeof(int64_t) * (nsuper + 1));
+    mix(s, sizeof(int32_t) * pi[nsuper]);
+    mix(perm, sizeof(int32_t) * n);
+    const bool same = F.present && F.sig == sig && F.lu == (xu != nullptr);
+    double *keep_panel = nullptr, *keep_panelU = nullptr;
+    int32_t *keep_rowidx = nullptr;
+    if (same) {
+        keep_panel = F.panel;
+        keep_panelU = F.panelU;
+        keep_rowidx = F.rowidx;
+        F.panel = F.panelU = nullptr;
+        F.rowidx = nullptr;
+    }
     if (F.present) free_factor(F);
+    F.sig = sig;
+    F.rowidx = keep_rowidx;
     F.n = n;
     F.lu = xu != nullptr;
     const bool lu = F.lu;
@@ -695,14 +729,16 @@ static int upload_factor_impl(ddm_ctx *c, int32_t sub, int32_t n, int32_t nsuper
         }
     }
     CK(dev_upload(&dconv, conv.data(), conv.size()));
-    CU(cudaMalloc((void **)&F.panel, sizeof(double) * std::max<int64_t>(1, tile_doubles)));
+    if (keep_panel) F.panel = keep_panel;
+    else CU(cudaMalloc((void **)&F.panel, sizeof(double) * std::max<int64_t>(1, tile_doubles)));
     if (!conv.empty()) {
         const int64_t nt = (int64_t)conv.size();
         LAUNCH(c, convert_tiles_kernel, nblocks(nt * 32), 256, nt, dconv, raw, daux, F.panel);
     }
     if (lu) {
         CK(dev_upload(&dconvU, convU.data(), convU.size()));
-        CU(cudaMalloc((void **)&F.panelU, sizeof(double) * std::max<int64_t>(1, utile_doubles)));
+        if (keep_panelU) F.panelU = keep_panelU;
+        else CU(cudaMalloc((void **)&F.panelU, sizeof(double) * std::max<int64_t>(1, utile_doubles)));
         if (!convU.empty()) {
             const int64_t nt = (int64_t)convU.size();
             LAUNCH(c, convert_tiles_kernel, nblocks(nt * 32), 256, nt, dconvU, rawU, daux, F.panelU);
@@ -716,7 +752,7 @@ static int upload_factor_impl(ddm_ctx *c, int32_t sub, int32_t n, int32_t nsuper
     cudaFree(dconv);
     cudaFree(dconvU);
     F.present = true;
-    c->finalized = false;
+    if (!same) c->finalized = false;
     return 0;
 }
 
@@ -1350,7 +1386,9 @@ extern "C" int ddm_twolevel_apply(ddm_ctx *c, int type, int mode, int with_coars
         // one restriction and one prolongation serve both levels (the reference does each twice)
         // the coarse solve (a few latency-bound launches) runs on the side stream beside the sweeps
         CK(restrict_all(c, d->d, 1));
-        const bool side = getenv("DDM_NO_SIDE_STREAM") == nullptr;
+        // (one rank only: with several ranks the coarse all-reduce would sit on SMs the cooperative backward sweep needs and
+        // couple its start to the slowest rank -- measured at 4 GPUs: backward sweep 0.74 -> 1.04 ms)
+        const bool side = c->nranks == 1 && getenv("DDM_NO_SIDE_STREAM") == nullptr;
         if (side) {
             CU(cudaEventRecord(c->ev_fork, c->s));
             CU(cudaStreamWaitEvent(c->s2, c->ev_fork, 0));
@@ -1373,6 +1411,18 @@ extern "C" int ddm_twolevel_apply(ddm_ctx *c, int type, int mode, int with_coars
     CK(restrict_all(c, dn, 1));
     CK(coarse_solve(c));
     return prolong(c, x->d, 0, 0, 1, 1);
+}
+
+extern "C" int ddm_galerkin_assemble(ddm_ctx *c, double *A0_out);
+extern "C" int ddm_update_coarse_matrix(ddm_ctx *c, const double *A0)
+{
+    CU(cudaSetDevice(c->device));
+    if (c->N0 <= 0 || !c->A0) return fail("no coarse space uploaded");
+    if (!A0) return ddm_galerkin_assemble(c, nullptr);
+    CU(cudaMemcpy(c->A0, A0, sizeof(double) * (size_t)c->N0 * c->N0, cudaMemcpyHostToDevice));
+    CK(coarse_factor(c, A0));
+    c->A0_pending = false;
+    return 0;
 }
 
 // N1: the Galerkin product A0 = Z^T A Z on the device, column by column with the solve-phase kernels:

@@ -119,6 +119,25 @@ class Context:
         pou = np.concatenate([P.pou[i] for i in range(a, b)]).astype(np.float64) if b > a else np.zeros(0)
         check(lib.ddm_upload_decomposition(self.h, C.c_int32(b - a), _p(S.sub_ptr, C.c_int64), _p(S.sub_dofs, C.c_int32),
                                            _p(pou, C.c_double)))
+        self.upload_factors(P, a, b)
+        N0 = int(P.A0.shape[0])
+        self.N0 = N0 if with_coarse else 0
+        if with_coarse and N0 > 0:
+            k = np.array([P.Z[i].shape[1] for i in range(a, b)], dtype=np.int32)
+            Z = np.concatenate([P.Z[i].ravel(order="F") for i in range(a, b)]) if b > a else np.zeros(1)
+            A0 = np.ascontiguousarray(P.A0, dtype=np.float64)
+            check(lib.ddm_upload_coarse(self.h, _p(k, C.c_int32), _p(np.ascontiguousarray(Z), C.c_double), C.c_int32(N0),
+                                        C.c_int32(S.k_offset), None if device_galerkin else _p(A0, C.c_double)))
+        check(lib.ddm_finalize(self.h))
+        if with_coarse and N0 > 0 and device_galerkin:
+            self.A0_device = np.empty((N0, N0))
+            check(lib.ddm_galerkin_assemble(self.h, _p(self.A0_device, C.c_double)))
+        return self
+
+    def upload_factors(self, P, a, b):
+        """ddm_upload_factor / ddm_upload_factor_lu for the hosted subdomains [a, b).  Re-uploading a factor with the same
+        symbolic structure only converts the new values in place (device schedules stay valid)."""
+        lib = self.lib
         for i in range(a, b):
             F = P.factors[i]
             if hasattr(F, "xu"):  # non-symmetric subdomain matrix: LU factor (the reference's UMFPack branch, schwarz.hh:85-92)
@@ -138,19 +157,6 @@ class Context:
                                         _p(np.ascontiguousarray(F.s, dtype=np.int32), C.c_int32),
                                         _p(np.ascontiguousarray(F.x, dtype=np.float64), C.c_double),
                                         _p(np.ascontiguousarray(F.perm, dtype=np.int32), C.c_int32)))
-        N0 = int(P.A0.shape[0])
-        self.N0 = N0 if with_coarse else 0
-        if with_coarse and N0 > 0:
-            k = np.array([P.Z[i].shape[1] for i in range(a, b)], dtype=np.int32)
-            Z = np.concatenate([P.Z[i].ravel(order="F") for i in range(a, b)]) if b > a else np.zeros(1)
-            A0 = np.ascontiguousarray(P.A0, dtype=np.float64)
-            check(lib.ddm_upload_coarse(self.h, _p(k, C.c_int32), _p(np.ascontiguousarray(Z), C.c_double), C.c_int32(N0),
-                                        C.c_int32(S.k_offset), None if device_galerkin else _p(A0, C.c_double)))
-        check(lib.ddm_finalize(self.h))
-        if with_coarse and N0 > 0 and device_galerkin:
-            self.A0_device = np.empty((N0, N0))
-            check(lib.ddm_galerkin_assemble(self.h, _p(self.A0_device, C.c_double)))
-        return self
 
     # -- helpers
     def vector(self, values=None):

@@ -1,0 +1,130 @@
+"""One-stop two-level Schwarz solver over the C ABI: the counterpart of the reference's public façade
+TwoLevelSchwarzSolver (/root/reference/dune/ddm/twolevel_schwarz.hh:27-146).
+
+The first apply() builds everything from the assembled matrix: non-overlapping sets (owner = lowest rank,
+pdelab_helper.hh:44-82), overlap growth, partition of unity, the POU coarse space from the template vectors {1, x, y, xy}
+(twolevel_schwarz.hh:47-51,107), subdomain factorisation, upload; the Galerkin matrix is assembled on the GPU
+(ddm_galerkin_assemble).  Every later apply() with a matrix of the same pattern only refreshes values
+(twolevel_schwarz.hh:99-104): operator values, numeric re-factorisation into the existing device tiles, coarse matrix -- index
+sets, bases, schedules and device allocations are kept.  Solver and preconditioner options follow the reference's
+ParameterTree keys (overlap, mode, fine.type, solver.type/restart/maxit; defaults :117-123: GMRES(30), maxit 1000).
+One GPU per solver object.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import multiprocessing as mp
+import os
+
+import numpy as np
+import scipy.sparse as sp
+
+from . import api
+from .lib import DDMError, check
+from .setup import coarse as coarse_mod
+from .setup import decomp, factor
+from .setup.problem import SetupProducts
+
+_G: dict = {}
+
+
+def _factor_job(i):
+    from threadpoolctl import threadpool_limits
+
+    with threadpool_limits(1):
+        s = _G["subs"][i]
+        Ai = _G["A"][s][:, s].tocsr()
+        Ai.sort_indices()
+        fn = factor.cholesky_supernodal if _G["symmetric"] else factor.lu_supernodal
+        return i, fn(Ai, _G["coords"][s], 32)
+
+
+class TwoLevelSchwarzSolver:
+    def __init__(self, coords, dof_cells, cell_part, nsub, config=None, symmetric=True, dirichlet=None, device=0, workers=None):
+        """coords: (n, d) DOF coordinates; dof_cells: (m, k) DOFs of every element; cell_part: subdomain of every element."""
+        cfg = dict(overlap=1, mode="additive", **{"fine.type": "restricted", "solver.type": "restartedgmressolver",
+                                                   "solver.restart": 30, "solver.maxit": 1000, "pou.type": "distance", "pou.shrink": 0})
+        cfg.update(config or {})
+        if cfg["solver.type"] not in ("restartedgmressolver", "cgsolver"):
+            raise DDMError(f"Unknown solver type '{cfg['solver.type']}'")
+        self.cfg, self.coords, self.cells, self.part, self.nsub = cfg, np.asarray(coords), np.asarray(dof_cells), np.asarray(cell_part), int(nsub)
+        self.symmetric, self.device = bool(symmetric), device
+        self.dirichlet = np.zeros(self.coords.shape[0], dtype=bool) if dirichlet is None else np.asarray(dirichlet, dtype=bool)
+        self.workers = workers or min(self.nsub, os.cpu_count() or 1)
+        self.ctx = None
+        self.P = None
+        self.res = None
+        self.updates = 0
+
+    # -- setup pieces
+    def _factors(self, A):
+        _G.clear()
+        _G.update(A=A, subs=self.P.subs if self.P else self._subs, coords=self.coords, symmetric=self.symmetric)
+        out = [None] * self.nsub
+        if self.workers > 1:
+            with mp.get_context("fork").Pool(self.workers) as pool:
+                for i, F in pool.imap_unordered(_factor_job, range(self.nsub)):
+                    out[i] = F
+        else:
+            for i in range(self.nsub):
+                out[i] = _factor_job(i)[1]
+        _G.clear()
+        return out
+
+    def _first(self, A, b):
+        n = A.shape[0]
+        cfg = self.cfg
+        novlp, owner = decomp.nonoverlapping_sets(n, self.cells, self.part, self.nsub)
+        self._subs = subs = decomp.grow_overlap(A, novlp, cfg["overlap"])
+        bm = decomp.boundary_masks(A, subs)
+        pou = decomp.partition_of_unity(A, subs, bm, owner, cfg["pou.type"], cfg["pou.shrink"], cfg["overlap"])
+        Z = [coarse_mod.pou_template_basis(self.coords[s], pou[i], self.dirichlet[s]) for i, s in enumerate(subs)]
+        factors = self._factors(A)
+        N0 = sum(z.shape[1] for z in Z)
+        self.P = SetupProducts(A=A, b=b, owner=owner, subs=subs, pou=pou, factors=factors, Z=Z, A0=np.zeros((N0, N0)),
+                               n_novlp=np.array([v.size for v in novlp], dtype=np.int64), coords=self.coords, dirichlet=self.dirichlet,
+                               meta=dict(nsub=self.nsub, symmetric=self.symmetric))
+        self.ctx = api.Context.from_products(self.P, device=self.device, device_galerkin=True)
+        self.P.A0 = self.ctx.A0_device
+
+    def _update(self, A):
+        P, ctx = self.P, self.ctx
+        if A.shape != P.A.shape or not (np.array_equal(A.indptr, P.A.indptr) and np.array_equal(A.indices, P.A.indices)):
+            raise DDMError("TwoLevelSchwarzSolver: the matrix pattern changed; build a new solver")
+        P.A = A
+        check(ctx.lib.ddm_update_operator_values(ctx.h, api._p(np.ascontiguousarray(A.data, dtype=np.float64), C.c_double)))
+        P.factors = self._factors(A)
+        ctx.upload_factors(P, 0, self.nsub)
+        check(ctx.lib.ddm_update_coarse_matrix(ctx.h, None))  # A0 re-assembled on the device from the new operator values
+        self.updates += 1
+
+    # -- the reference's entry point: apply(A, z, r, reduction)
+    def apply(self, A, z, r, reduction):
+        """Solve A z = r to the given defect reduction; z holds the initial guess and receives the solution, r is left as the
+        defect (Dune::InverseOperator convention).  Returns the InverseOperatorResult (also kept in self.res)."""
+        A = sp.csr_matrix(A)
+        A.sort_indices()
+        if self.ctx is None:
+            self._first(A, np.array(r, dtype=np.float64))
+        else:
+            self._update(A)
+        ctx, cfg = self.ctx, self.cfg
+        op, spr = api.NonOverlappingOperator(ctx), api.NonOverlappingScalarProduct(ctx)
+        prec = api.CombinedPreconditioner(cfg["mode"])
+        prec.set_op(op)
+        prec.add(api.SchwarzPreconditioner(ctx, cfg["fine.type"]))
+        prec.add(api.GalerkinPreconditioner(ctx))
+        if cfg["solver.type"] == "cgsolver":
+            solver = api.CGSolver(op, spr, prec, reduction=reduction, maxit=cfg["solver.maxit"])
+        else:
+            solver = api.RestartedGMResSolver(op, spr, prec, reduction=reduction, restart=cfg["solver.restart"], maxit=cfg["solver.maxit"])
+        x, b = ctx.vector(np.asarray(z, dtype=np.float64)), ctx.vector(np.asarray(r, dtype=np.float64))
+        self.res = solver.solve_device(x, b)
+        z[:] = x.download()
+        r[:] = b.download()
+        return self.res
+
+    def close(self):
+        if self.ctx is not None:
+            self.ctx.close()
+            self.ctx = None

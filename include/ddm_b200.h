@@ -121,6 +121,15 @@ int ddm_finalize(ddm_ctx *ctx);
  * is then factored like an uploaded one.  A0_out (N0 x N0 row-major, may be NULL) receives a copy. */
 int ddm_galerkin_assemble(ddm_ctx *ctx, double *A0_out);
 
+/* ---- value updates with unchanged structure (Newton loops) -------------------------------
+ * TwoLevelSchwarzSolver::apply keeps the overlapping index sets and only refreshes matrix values on every call after
+ * the first (dune/ddm/twolevel_schwarz.hh:99-104).  Here: new operator values in the uploaded sparsity pattern; a
+ * ddm_upload_factor / ddm_upload_factor_lu call whose symbolic arrays equal the uploaded ones converts the new panels in
+ * place and keeps the device schedules (no ddm_finalize needed); the coarse matrix is replaced (A0 != NULL) or
+ * re-assembled on the device from the new operator (A0 == NULL). */
+int ddm_update_operator_values(ddm_ctx *ctx, const double *val);
+int ddm_update_coarse_matrix(ddm_ctx *ctx, const double *A0);
+
 /* ---- vectors: the operations Dune's Krylov solvers need from X --------------------------
  * (extern/dune-istl/dune/istl/solvers.hh:292-335,933-1012: copy, =scalar, =X, axpy, *=, +=) */
 int ddm_vec_create(ddm_ctx *ctx, ddm_vec **out);
