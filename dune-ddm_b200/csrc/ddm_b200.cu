@@ -172,6 +172,7 @@ struct ddm_ctx {
     double *h_scal = nullptr;                   // pinned
     double *h_stage = nullptr;                  // pinned staging for *_host entry points (2*n_own)
     ddm_vec *hv[3] = {nullptr, nullptr, nullptr};
+    std::vector<cudaEvent_t> stage_ev;          // one per staging chunk (stage_out)
     ddm_vec *tmp[4] = {nullptr, nullptr, nullptr, nullptr};
     std::vector<ddm_vec *> gm_v;  // GMRES basis v[0..m], w, b2 (allocated on first use)
     double *gm_h = nullptr, *gm_hh = nullptr;  // one column of H: device, pinned host
@@ -293,6 +294,7 @@ extern "C" int ddm_ctx_destroy(ddm_ctx *c)
     for (void *p : ptrs) cudaFree(p);
     cudaFreeHost(c->h_scal);
     cudaFreeHost(c->h_stage);
+    for (auto e : c->stage_ev) cudaEventDestroy(e);
     for (auto &r : c->trecs) {
         cudaEventDestroy(r.a);
         cudaEventDestroy(r.b);
@@ -1653,19 +1655,39 @@ extern "C" int ddm_gmres_solve(ddm_ctx *c, ddm_vec *b, ddm_vec *x, double reduct
 }
 
 // ------------------------------------------------------------------------------------------------ host-pointer forms
+// Host vectors are pageable: they pass through the pinned staging area in 2 MB pieces so that the CPU copy of one piece
+// overlaps the DMA of the previous one.
+constexpr int64_t kStageChunk = 1 << 18;
 static int stage_in(ddm_ctx *c, ddm_vec *v, const double *h, int slot)
 {
     double *st = c->h_stage + (int64_t)slot * c->n_own;
-    memcpy(st, h, sizeof(double) * c->n_own);
-    CU(cudaMemcpyAsync(v->d, st, sizeof(double) * c->n_own, cudaMemcpyHostToDevice, c->s));
+    for (int64_t o = 0; o < c->n_own; o += kStageChunk) {
+        const int64_t m = std::min(kStageChunk, c->n_own - o);
+        memcpy(st + o, h + o, sizeof(double) * m);
+        CU(cudaMemcpyAsync(v->d + o, st + o, sizeof(double) * m, cudaMemcpyHostToDevice, c->s));
+    }
     return 0;
 }
 static int stage_out(ddm_ctx *c, const ddm_vec *v, double *h, int slot)
 {
     double *st = c->h_stage + (int64_t)slot * c->n_own;
-    CU(cudaMemcpyAsync(st, v->d, sizeof(double) * c->n_own, cudaMemcpyDeviceToHost, c->s));
+    const int64_t nchunk = (c->n_own + kStageChunk - 1) / kStageChunk;
+    while ((int64_t)c->stage_ev.size() < nchunk) {
+        cudaEvent_t e;
+        CU(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+        c->stage_ev.push_back(e);
+    }
+    for (int64_t k = 0; k < nchunk; ++k) {
+        const int64_t o = k * kStageChunk, m = std::min(kStageChunk, c->n_own - o);
+        CU(cudaMemcpyAsync(st + o, v->d + o, sizeof(double) * m, cudaMemcpyDeviceToHost, c->s));
+        CU(cudaEventRecord(c->stage_ev[k], c->s));
+    }
+    for (int64_t k = 0; k < nchunk; ++k) {
+        const int64_t o = k * kStageChunk, m = std::min(kStageChunk, c->n_own - o);
+        CU(cudaEventSynchronize(c->stage_ev[k]));
+        memcpy(h + o, st + o, sizeof(double) * m);
+    }
     CU(cudaStreamSynchronize(c->s));
-    memcpy(h, st, sizeof(double) * c->n_own);
     return 0;
 }
 extern "C" int ddm_op_apply_host(ddm_ctx *c, const double *x, double *y)

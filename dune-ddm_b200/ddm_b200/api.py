@@ -396,11 +396,17 @@ class CGSolver:
                                       C.c_int(self.prec.mode), C.c_int(int(len(self.prec.precs) > 1)), C.byref(res), _p(hist, C.c_double)))
         return InverseOperatorResult(res.iterations, bool(res.converged), res.reduction, res.conv_rate, res.elapsed, hist[: res.iterations + 1])
 
-    def solve_host(self, b_host, x_host=None):
-        """End-to-end call with host buffers (H2D and D2H inside)."""
+    def solve_host(self, b_host, x_host=None, overwrite=False):
+        """End-to-end call with host buffers (H2D and D2H inside).  overwrite=True works in the caller's float64 arrays, as
+        Dune::CGSolver::apply does (b becomes the defect, x the solution); otherwise copies are made first."""
         s = self.prec.precs[0]
-        b = np.array(b_host, dtype=np.float64)
-        x = np.zeros_like(b) if x_host is None else np.array(x_host, dtype=np.float64)
+        if overwrite and x_host is not None:
+            b, x = b_host, x_host
+            if not (b.dtype == np.float64 and x.dtype == np.float64 and b.flags.c_contiguous and x.flags.c_contiguous):
+                raise DDMError("solve_host(overwrite=True) needs contiguous float64 arrays")
+        else:
+            b = np.array(b_host, dtype=np.float64)
+            x = np.zeros_like(b) if x_host is None else np.array(x_host, dtype=np.float64)
         res = Result()
         hist = np.zeros(self.maxit + 1)
         check(s.ctx.lib.ddm_pcg_solve_host(s.ctx.h, _p(b, C.c_double), _p(x, C.c_double), C.c_double(self.reduction), C.c_int32(self.maxit),
