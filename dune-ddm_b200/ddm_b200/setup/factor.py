@@ -310,7 +310,9 @@ def lu_supernodal(A, coords=None, leaf_size=32):
     for the diffusion-dominated DG matrices this path is used for).
     """
     n = A.shape[0]
-    S = (abs(A) + abs(A).T).tocsr()
+    Ac0 = A.tocsr()
+    Pat = sp.csr_matrix((np.ones(Ac0.nnz), Ac0.indices, Ac0.indptr), shape=Ac0.shape)  # stored entries, explicit zeros included
+    S = (Pat + Pat.T).tocsr()
     perm, first = nested_dissection(S, coords, leaf_size)
     nsuper = first.size - 1
     Ap = A.tocsr()[perm][:, perm]
