@@ -276,14 +276,16 @@ __global__ void coarse_restrict_final_kernel(int nsub, const int32_t *__restrict
 // K6  dense coarse solve as matrix-vector products with the explicit inverse (plus one refinement step
 // driven from the host side): out = M v, M row-major N x N, one warp per row.
 __global__ void __launch_bounds__(256) dense_gemv_kernel(int N, const double *__restrict__ M, const double *__restrict__ v,
-                                                         double *out, const double *addto, double sign)
+                                                         double *out, const double *addto, double sign, int tri)
 {
+    // tri 0: full rows; 1: lower triangle (columns <= row); 2: upper triangle (columns >= row, start aligned down to 32)
     const int row = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const int lane = threadIdx.x & 31;
     if (row >= N) return;
     const double *Mr = M + (int64_t)row * N;
+    const int j0 = tri == 2 ? (row & ~31) : 0, j1 = tri == 1 ? row + 1 : N;
     double acc = 0.0;
-    for (int j = lane; j < N; j += 32) acc = fma(Mr[j], __ldg(v + j), acc);
+    for (int j = j0 + lane; j < j1; j += 32) acc = fma(Mr[j], __ldg(v + j), acc);
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(kFull, acc, o);
     if (lane == 0) out[row] = addto ? addto[row] + sign * acc : sign * acc;
@@ -337,5 +339,43 @@ __global__ void __launch_bounds__(256) gather_sum_kernel(int64_t nloc, const int
     x[v] = accumulate ? x[v] + acc : acc;
 }
 
+
+// ------------------------------------------------------------------------------------------------
+// Segmented vector operations over the subdomain ranges of a block-diagonal problem (all subdomains advance in lock
+// step): the recurrences of the batched shift-invert Lanczos used for the GenEO eigenproblems (SURVEY 8f N3;
+// replaces one Spectra SymGEigsShiftSolver run per rank, dune/ddm/eigensolvers/spectra.hh:112-215).
+// Segments are the <= kSeg-long pieces of the subdomain ranges built at finalize.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) seg_dot_partial_kernel(const Segment *__restrict__ segs, const double *__restrict__ x,
+                                                              const double *__restrict__ y, double *__restrict__ partial)
+{
+    __shared__ double sm[8];
+    const Segment sg = segs[blockIdx.x];
+    double acc = 0.0;
+    for (int t = threadIdx.x; t < sg.len; t += blockDim.x) acc = fma(x[sg.start + t], y[sg.start + t], acc);
+    const double r = block_sum_256(acc, sm);
+    if (threadIdx.x == 0) partial[blockIdx.x] = r;
+}
+__global__ void seg_dot_final_kernel(int nsub, const int32_t *__restrict__ seg_ptr, const double *__restrict__ partial,
+                                     double *__restrict__ out)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nsub) return;
+    double acc = 0.0;
+    for (int s = seg_ptr[i]; s < seg_ptr[i + 1]; ++s) acc += partial[s];
+    out[i] = acc;
+}
+// y[p] = beta[sub(p)] * y[p] + alpha[sub(p)] * x[p]   (beta == nullptr: 1)
+__global__ void __launch_bounds__(256) seg_axpby_kernel(const Segment *__restrict__ segs, const double *__restrict__ alpha,
+                                                        const double *__restrict__ x, const double *__restrict__ beta,
+                                                        double *__restrict__ y)
+{
+    const Segment sg = segs[blockIdx.x];
+    const double a = alpha[sg.sub], b = beta ? beta[sg.sub] : 1.0;
+    for (int t = threadIdx.x; t < sg.len; t += blockDim.x) {
+        const int p = sg.start + t;
+        y[p] = fma(a, x[p], b * y[p]);
+    }
+}
 
 } // namespace ddm

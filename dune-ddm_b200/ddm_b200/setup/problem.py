@@ -98,6 +98,13 @@ def _sub_job(i):
         dl = g["dirichlet"][s]
         if kind == "geneo":
             An, Bn = coarse_mod.neumann_matrices(A.shape[0], g["cells"], g["Ke"], s, g["shared"], g["dirichlet"])
+            if g["eigensolver"] == "gpu":
+                # batched device eigensolve (setup/geneo_gpu.py): this worker only factors K_i = A_neu + shift C_i
+                from . import geneo_gpu
+
+                Cm = geneo_gpu.weighted_overlap_matrix(Bn, g["pou"][i])
+                FK = factor.cholesky_supernodal((An + g["shift"] * Cm).tocsr(), co, g["leaf_size"])
+                return i, F, (Cm, FK)
             Zi, ev = coarse_mod.geneo_basis(An, Bn, g["pou"][i], dl, nev=g["nev"], shift=g["shift"], tol=g["eig_tol"])
         elif kind == "pou":
             Zi = coarse_mod.pou_template_basis(g["coords"][s], g["pou"][i], dl)
@@ -110,7 +117,7 @@ def _sub_job(i):
 
 def build(coords, cells, Ke, dirichlet, rhs, cell_part, nsub, overlap=2, pou_kind="distance", shrink=0,
           coarse="geneo", nev=16, shift=1e-3, eig_tol=1e-5, leaf_size=32, workers=None, meta=None, only=None, gather=None,
-          A_full=None, symmetric=True, ke_fn=None):
+          A_full=None, symmetric=True, ke_fn=None, eigensolver="host", eig_device=0):
     """Generic pipeline from an element-wise description to SetupProducts.
 
     only / gather: with several processes (one per GPU) every process factors and builds the coarse basis of its own
@@ -165,7 +172,8 @@ def build(coords, cells, Ke, dirichlet, rhs, cell_part, nsub, overlap=2, pou_kin
         cells, Ke = cells[keep], ke_fn(keep)
     _G.clear()
     _G.update(A=A, subs=subs, coords=coords, cells=cells, Ke=Ke, dirichlet=dirichlet, shared=shared, pou=pou,
-              coarse=coarse, nev=nev, shift=shift, eig_tol=eig_tol, leaf_size=leaf_size, symmetric=symmetric)
+              coarse=coarse, nev=nev, shift=shift, eig_tol=eig_tol, leaf_size=leaf_size, symmetric=symmetric,
+              eigensolver=eigensolver if coarse == "geneo" else "host")
     workers = workers or min(max(len(todo), 1), os.cpu_count() or 1)
     factors = [None] * nsub
     Z = [None] * nsub
@@ -177,6 +185,14 @@ def build(coords, cells, Ke, dirichlet, rhs, cell_part, nsub, overlap=2, pou_kin
         for i in todo:
             _, factors[i], Z[i] = _sub_job(i)
     _G.clear()
+    if coarse == "geneo" and eigensolver == "gpu" and todo:
+        tick("factor A_i and K_i")
+        from . import geneo_gpu
+
+        Zs, _ = geneo_gpu.batched_geneo([Z[i][0] for i in todo], [Z[i][1] for i in todo], [pou[i] for i in todo],
+                                        [dirichlet[subs[i]] for i in todo], nev=nev, shift=shift, tol=eig_tol, device=eig_device)
+        for i, Zi in zip(todo, Zs):
+            Z[i] = Zi
     tick("factor + coarse basis")
     if gather is None:
         A0, off, _ = coarse_mod.galerkin_matrix(A, subs, Z)

@@ -130,6 +130,18 @@ int ddm_galerkin_assemble(ddm_ctx *ctx, double *A0_out);
 int ddm_update_operator_values(ddm_ctx *ctx, const double *val);
 int ddm_update_coarse_matrix(ddm_ctx *ctx, const double *A0);
 
+/* ---- batched GenEO eigensolve support (setup) -------------------------------
+ * For a block-diagonal context (operator = blockdiag(C_i), subdomain i = the contiguous vector range
+ * [sub_ptr[i], sub_ptr[i+1]), factors of K_i = A_neu,i + shift C_i) all subdomains run the shift-invert Lanczos
+ * recurrence of their generalised eigenproblem A_neu v = lambda C v in lock step (the reference runs one
+ * Spectra::SymGEigsShiftSolver per rank, dune/ddm/eigensolvers/spectra.hh:112-215, coarse_spaces.hh:319-331):
+ * ddm_blockdiag_solve applies all K_i^{-1} with the triangular-sweep kernels, ddm_op_apply all C_i, and the two
+ * segmented operations below do the per-subdomain inner products and updates. */
+int ddm_blockdiag_solve(ddm_ctx *ctx, ddm_vec *d, ddm_vec *x);
+int ddm_seg_dot(ddm_ctx *ctx, const ddm_vec *x, const ddm_vec *y, double *out_per_subdomain);
+int ddm_seg_axpby(ddm_ctx *ctx, const double *alpha_per_subdomain, const ddm_vec *x, const double *beta_per_subdomain_or_null,
+                  ddm_vec *y);
+
 /* ---- vectors: the operations Dune's Krylov solvers need from X --------------------------
  * (extern/dune-istl/dune/istl/solvers.hh:292-335,933-1012: copy, =scalar, =X, axpy, *=, +=) */
 int ddm_vec_create(ddm_ctx *ctx, ddm_vec **out);
