@@ -14,6 +14,7 @@
 #ifndef DUNE_DDM_B200_ADAPTORS_HH
 #define DUNE_DDM_B200_ADAPTORS_HH
 
+#include <algorithm>
 #include <memory>
 #include <string>
 #include <vector>
@@ -58,15 +59,59 @@ public:
     ddm_ctx *c = ctx->c_;
     const std::int64_t n = p.scalar("n");
     const std::int32_t nsub = (std::int32_t)p.scalar("nsub");
-    check(ddm_upload_operator(c, n, 0, p["A_rowptr"].as<std::int64_t>(), p["A_col"].as<std::int32_t>(), p["A_val"].as<double>()));
+    if (p.has("block") && p.scalar("block") == 3) {
+      // node-major 3x3 blocks (BCRSMatrix<FieldMatrix<double,3,3>>): scalar CSR of the pack -> block CSR
+      const std::int64_t *rp = p["A_rowptr"].as<std::int64_t>();
+      const std::int32_t *ci = p["A_col"].as<std::int32_t>();
+      const double *va = p["A_val"].as<double>();
+      const std::int64_t nb = n / 3;
+      std::vector<std::int64_t> brp(nb + 1, 0);
+      std::vector<std::int32_t> bci;
+      std::vector<double> bva;
+      std::vector<std::int64_t> slot(nb, -1);
+      for (std::int64_t I = 0; I < nb; ++I) {
+        const std::size_t first = bci.size();
+        for (int r = 0; r < 3; ++r)
+          for (std::int64_t k = rp[3 * I + r]; k < rp[3 * I + r + 1]; ++k) {
+            const std::int32_t J = ci[k] / 3;
+            if (slot[J] < (std::int64_t)first) {
+              slot[J] = (std::int64_t)bci.size();
+              bci.push_back(J);
+              bva.insert(bva.end(), 9, 0.0);
+            }
+            bva[9 * slot[J] + 3 * r + ci[k] % 3] = va[k];
+          }
+        // ascending block columns, as BCRSMatrix stores them
+        std::vector<std::size_t> ord(bci.size() - first);
+        for (std::size_t q = 0; q < ord.size(); ++q) ord[q] = first + q;
+        std::sort(ord.begin(), ord.end(), [&](std::size_t a, std::size_t b) { return bci[a] < bci[b]; });
+        std::vector<std::int32_t> cs;
+        std::vector<double> vs;
+        for (std::size_t q : ord) {
+          cs.push_back(bci[q]);
+          vs.insert(vs.end(), bva.begin() + 9 * q, bva.begin() + 9 * q + 9);
+        }
+        std::copy(cs.begin(), cs.end(), bci.begin() + first);
+        std::copy(vs.begin(), vs.end(), bva.begin() + 9 * first);
+        for (std::size_t q = first; q < bci.size(); ++q) slot[bci[q]] = -1;
+        brp[I + 1] = (std::int64_t)bci.size();
+      }
+      check(ddm_upload_operator_bcsr3(c, nb, 0, brp.data(), bci.data(), bva.data()));
+    } else
+      check(ddm_upload_operator(c, n, 0, p["A_rowptr"].as<std::int64_t>(), p["A_col"].as<std::int32_t>(), p["A_val"].as<double>()));
     check(ddm_upload_decomposition(c, nsub, p["sub_ptr"].as<std::int64_t>(), p["sub_dofs"].as<std::int32_t>(), p["pou"].as<double>()));
     const std::int64_t *sp = p["sub_ptr"].as<std::int64_t>();
     for (std::int32_t i = 0; i < nsub; ++i) {
       const std::string f = "F" + std::to_string(i) + "_";
       const auto &su = p[f + "super"];
-      check(ddm_upload_factor(c, i, (std::int32_t)(sp[i + 1] - sp[i]), (std::int32_t)su.count() - 1, su.as<std::int32_t>(),
-                              p[f + "pi"].as<std::int64_t>(), p[f + "px"].as<std::int64_t>(), p[f + "s"].as<std::int32_t>(),
-                              p[f + "x"].as<double>(), p[f + "perm"].as<std::int32_t>()));
+      if (p.has(f + "xu"))  // LU factor of a non-symmetric subdomain matrix (the reference's UMFPack branch)
+        check(ddm_upload_factor_lu(c, i, (std::int32_t)(sp[i + 1] - sp[i]), (std::int32_t)su.count() - 1, su.as<std::int32_t>(),
+                                   p[f + "pi"].as<std::int64_t>(), p[f + "px"].as<std::int64_t>(), p[f + "s"].as<std::int32_t>(),
+                                   p[f + "x"].as<double>(), p[f + "xu"].as<double>(), p[f + "perm"].as<std::int32_t>()));
+      else
+        check(ddm_upload_factor(c, i, (std::int32_t)(sp[i + 1] - sp[i]), (std::int32_t)su.count() - 1, su.as<std::int32_t>(),
+                                p[f + "pi"].as<std::int64_t>(), p[f + "px"].as<std::int64_t>(), p[f + "s"].as<std::int32_t>(),
+                                p[f + "x"].as<double>(), p[f + "perm"].as<std::int32_t>()));
     }
     const std::int32_t N0 = (std::int32_t)p["A0"].dims.at(0);
     if (with_coarse && N0 > 0)
