@@ -21,24 +21,26 @@ from ddm_b200.setup import problem
 def main():
     rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ.get("LOCAL_RANK", 0))
     torch.cuda.set_device(local)
-    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    # torch.distributed only moves host data here (unique id, assembled results): gloo, as in bench.py.  The data path's NCCL
+    # communicator lives inside libddm_b200.so; a second (torch) NCCL communicator in the same process is avoided.
+    dist.init_process_group("gloo")
     ncell, nsub = int(os.environ.get("NCELL", 16)), int(os.environ.get("NSUB", 4 * world))
     P = problem.unitcube_p1(ncell, nsub, overlap=2, nev=6, workers=1)
     buf = (C.c_uint8 * 128)()
     if rank == 0:
         api.check(lib.load().ddm_comm_unique_id(buf))
-    t = torch.tensor(list(buf), dtype=torch.uint8, device="cuda")
+    t = torch.tensor(list(buf), dtype=torch.uint8)
     dist.broadcast(t, 0)
-    ctx = api.Context.from_products(P, device=local, rank=rank, world=world, unique_id=t.cpu().tolist())
+    ctx = api.Context.from_products(P, device=local, rank=rank, world=world, unique_id=t.tolist())
     op, sp = api.NonOverlappingOperator(ctx), api.NonOverlappingScalarProduct(ctx)
     rng = np.random.default_rng(11)
     d = rng.standard_normal(P.n)
 
     def gather(vec_own):
-        out = torch.zeros(P.n, dtype=torch.float64, device="cuda")
-        out[torch.from_numpy(ctx.shard.owned).cuda()] = torch.from_numpy(vec_own).cuda()
+        out = torch.zeros(P.n, dtype=torch.float64)
+        out[torch.from_numpy(ctx.shard.owned)] = torch.from_numpy(vec_own)
         dist.all_reduce(out)
-        return out.cpu().numpy()
+        return out.numpy()
 
     results = {}
     x, y = ctx.vector(ctx.owned(d)), ctx.vector()
@@ -78,7 +80,7 @@ def main():
             good = err <= t_
             ok &= bool(good)
             print(f"[{world} GPUs] {name}: {err:.3e} (tol {t_:.1e}) {'ok' if good else 'FAIL'}", flush=True)
-    flag = torch.tensor([1 if ok else 0], device="cuda")
+    flag = torch.tensor([1 if ok else 0])
     dist.broadcast(flag, 0)
     ctx.close()
     dist.destroy_process_group()

@@ -125,3 +125,63 @@ def test_sharded_spmv_and_halo_sum_in_lockstep(small3d, world):
         e.halo_reverse_add(c, lambda _s, _d, me=e.S.rank: {p: send[p][me] for p in send[me]})
         got[e.S.owned] = c[: e.S.n_own]
     assert np.allclose(got, want, rtol=0, atol=1e-13)
+
+
+def test_eight_ranks_all_to_all_halo_and_apply():
+    """The 2x2x2 rank layout of an 8-GPU box: every rank has all seven others as peers.  Halo plan symmetry and the rank-local
+    two-level sequence (emulated with threads exchanging in lock step) against the single-process oracle."""
+    import threading
+
+    from ddm_b200.setup import problem
+    from oracle import oracle
+    from shard_emulator import RankEmu
+
+    world = 8
+    P = problem.unitcube_p1(12, 32, overlap=2, nev=4, workers=1)
+    O = oracle.Oracle(P)
+    shards = [partition.shard(P, r, world) for r in range(world)]
+    assert max(S.peers.size for S in shards) == world - 1
+    for S in shards:
+        for k, p in enumerate(S.peers):
+            T = shards[int(p)]
+            kk = np.flatnonzero(T.peers == S.rank)
+            assert kk.size == 1  # peers are mutual: every send has its receive
+            sent = S.owned[S.send_idx[S.send_ptr[k] : S.send_ptr[k + 1]]]
+            assert np.array_equal(sent, T.ghosts[T.recv_ptr[kk[0]] : T.recv_ptr[kk[0] + 1]])
+    emus = [RankEmu(P, S, O) for S in shards]
+    bar, box = threading.Barrier(world), {}
+
+    def comm(rank):
+        def exchange(send, direction):
+            box[rank] = send
+            bar.wait()
+            out = {p: box[p][rank] for p in send}
+            bar.wait()
+            return out
+
+        def allreduce(v):
+            box[("a", rank)] = v.copy()
+            bar.wait()
+            tot = sum(box[("a", r)] for r in range(world))
+            bar.wait()
+            return tot
+
+        return exchange, allreduce
+
+    d = np.random.default_rng(3).standard_normal(P.n)
+    res = [None] * world
+
+    def run(r):
+        ex, ar = comm(r)
+        res[r] = emus[r].twolevel(emus[r].local(d[shards[r].owned]), ex, ar)
+
+    threads = [threading.Thread(target=run, args=(r,)) for r in range(world)]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join(timeout=120)
+    got = np.zeros(P.n)
+    for S, xr in zip(shards, res):
+        got[S.owned] = xr
+    want = O.twolevel_apply(d)
+    assert np.linalg.norm(got - want) <= 1e-10 * np.linalg.norm(want)
