@@ -58,6 +58,9 @@ def geneo_basis(A_neu, B_neu, pou, dirichlet_local, nev=16, shift=1e-3, tol=1e-5
     v0 = rng.standard_normal(n)
     # Shift to the left of the spectrum (all eigenvalues are >= 0): A + shift*C is SPD-like
     # and the eigenvalues nearest the shift are the smallest ones the reference asks for.
+    if C.nnz == 0 or abs(C).max() == 0.0:
+        # no overlap region (a single subdomain): the eigenproblem has no finite eigenvalue, the subdomain adds no coarse vector
+        return np.zeros((n, 0), order="F"), np.zeros(0)
     K = (A_neu + shift * C).tocsc()
     lu = spla.splu(K, permc_spec="MMD_AT_PLUS_A", diag_pivot_thresh=0.0, options=dict(SymmetricMode=True))
     OPinv = spla.LinearOperator((n, n), matvec=lu.solve, dtype=np.float64)

@@ -103,6 +103,8 @@ def _sub_job(i):
                 from . import geneo_gpu
 
                 Cm = geneo_gpu.weighted_overlap_matrix(Bn, g["pou"][i])
+                if Cm.nnz == 0 or abs(Cm).max() == 0.0:  # no overlap region: no coarse vector from this subdomain
+                    return i, F, np.zeros((s.size, 0), order="F")
                 FK = factor.cholesky_supernodal((An + g["shift"] * Cm).tocsr(), co, g["leaf_size"])
                 return i, F, (Cm, FK)
             Zi, ev = coarse_mod.geneo_basis(An, Bn, g["pou"][i], dl, nev=g["nev"], shift=g["shift"], tol=g["eig_tol"])
@@ -189,10 +191,12 @@ def build(coords, cells, Ke, dirichlet, rhs, cell_part, nsub, overlap=2, pou_kin
         tick("factor A_i and K_i")
         from . import geneo_gpu
 
-        Zs, _ = geneo_gpu.batched_geneo([Z[i][0] for i in todo], [Z[i][1] for i in todo], [pou[i] for i in todo],
-                                        [dirichlet[subs[i]] for i in todo], nev=nev, shift=shift, tol=eig_tol, device=eig_device)
-        for i, Zi in zip(todo, Zs):
-            Z[i] = Zi
+        batch = [i for i in todo if isinstance(Z[i], tuple)]
+        if batch:
+            Zs, _ = geneo_gpu.batched_geneo([Z[i][0] for i in batch], [Z[i][1] for i in batch], [pou[i] for i in batch],
+                                            [dirichlet[subs[i]] for i in batch], nev=nev, shift=shift, tol=eig_tol, device=eig_device)
+            for i, Zi in zip(batch, Zs):
+                Z[i] = Zi
     tick("factor + coarse basis")
     if gather is None:
         A0, off, _ = coarse_mod.galerkin_matrix(A, subs, Z)

@@ -122,3 +122,17 @@ def test_threaded_oracle_equals_serial(case):
     d = rng.standard_normal(P.n)
     O1 = oracle.Oracle(P, nthreads=1)
     assert np.array_equal(O1.twolevel_apply(d), O.twolevel_apply(d))
+
+
+def test_single_subdomain_is_a_direct_solve():
+    """Edge case: one subdomain (no overlap region, so GenEO contributes no coarse vector): the one-level method is the exact
+    inverse and CG converges in one step."""
+    from ddm_b200.setup import problem
+    from oracle import oracle
+
+    P = problem.unitcube_p1(6, 1, overlap=1, nev=3, workers=1)
+    assert P.A0.shape == (0, 0) and P.Z[0].shape[1] == 0
+    O = oracle.Oracle(P)
+    x, it, conv, _ = O.pcg(P.b, reduction=1e-8, maxit=10, with_coarse=False)
+    assert conv and it <= 2
+    assert np.linalg.norm(P.b - P.A @ x) <= 1e-10 * np.linalg.norm(P.b)
