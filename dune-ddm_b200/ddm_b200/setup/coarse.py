@@ -111,12 +111,40 @@ def galerkin_matrix(A, subs, bases):
 
 
 def galerkin_columns(A, subs, bases, mine):
-    """The columns of A0 = Z^T A Z that belong to the subdomains `mine` (a contiguous block): Z^T (A Z_mine)."""
-    _, off, Z = galerkin_matrix_operands(subs, bases, A.shape[0])
-    if not len(mine):
-        return np.zeros((int(off[-1]), 0))
+    """The columns of A0 = Z^T A Z that belong to the subdomains `mine` (a contiguous block), computed block by block from
+    the neighbours only -- block (i, j) = Z_i^T (A R_j^T Z_j) restricted to the rows both touch -- the way the reference's
+    build_solver exchanges A Z_j with the neighbouring ranks (galerkin_preconditioner.hh:258-328).  Never forms the global
+    n x N0 basis matrix."""
+    n = A.shape[0]
+    ks = np.array([b.shape[1] for b in bases], dtype=np.int64)
+    off = np.concatenate(([0], np.cumsum(ks)))
+    N0 = int(off[-1])
+    mine = list(mine)
+    if not mine:
+        return np.zeros((N0, 0))
     c0, c1 = int(off[min(mine)]), int(off[max(mine) + 1])
-    return (Z.T @ (A @ Z[:, c0:c1])).toarray()
+    out = np.zeros((N0, c1 - c0))
+    A = A.tocsr()
+    At = A.T.tocsr()
+    memb = sp.csr_matrix((np.ones(sum(s.size for s in subs), dtype=np.int8), (np.concatenate(subs), np.repeat(np.arange(len(subs)), [s.size for s in subs]))),
+                         shape=(n, len(subs)))
+    pos = np.full(n, -1, dtype=np.int64)
+    for j in mine:
+        if ks[j] == 0:
+            continue
+        sj = subs[j]
+        R = np.unique(At[sj].indices)  # rows of A with an entry in the columns s_j
+        Y = A[R][:, sj] @ bases[j]  # (|R|, k_j): the non-zero rows of A R_j^T Z_j
+        pos[R] = np.arange(R.size)
+        for i in np.unique(memb[R].indices):
+            if ks[i] == 0:
+                continue
+            idx = pos[subs[i]]
+            m = idx >= 0
+            if m.any():
+                out[off[i] : off[i + 1], off[j] - c0 : off[j + 1] - c0] = bases[i][m].T @ Y[idx[m]]
+        pos[R] = -1
+    return out
 
 
 def galerkin_matrix_operands(subs, bases, n):
