@@ -56,3 +56,45 @@ def test_sharded_setup_equals_single_process(tmp_path):
         assert [z.shape for z in r["Z"]] == [z.shape for z in P.Z]
         for i in r["have"]:
             assert r["x"][i].shape == P.factors[i].x.shape and np.allclose(r["x"][i], P.factors[i].x, rtol=1e-9, atol=1e-9 * np.abs(P.factors[i].x).max())
+
+
+BENCH_WORKER = r"""
+import os, sys
+sys.path.insert(0, {root!r}); sys.path.insert(0, os.path.join({root!r}, "dune-ddm_b200"))
+import torch.distributed as dist, numpy as np
+import bench
+from ddm_b200 import partition
+sys.argv = ["bench.py", "--ncell", "8", "--nsub", "8", "--gpus", os.environ["WORLD_SIZE"]]
+a = bench.parse()
+rank, world, local = bench.dist_env()
+dist.init_process_group("gloo")
+def gather(obj):
+    out = [None] * world
+    dist.all_gather_object(out, obj)
+    return out
+P = bench.build_problem(a, world, rank, gather)
+S = partition.shard(P, rank, world)
+have = [i for i, F in enumerate(P.factors) if F is not None]
+assert have == list(range(*S.sub_range)), (have, S.sub_range)
+assert P.nsub == 8 * world and P.A0.shape[0] == sum(z.shape[1] for z in P.Z)
+assert abs(P.A0 - P.A0.T).max() <= 1e-12 * abs(P.A0).max()
+sums = [None] * world
+dist.all_gather_object(sums, (float(abs(P.A0).sum()), float(abs(P.A).sum()), S.n_own))
+assert len(set(s[:2] for s in sums)) == 1 and sum(s[2] for s in sums) == P.n  # identical products on every rank
+dist.barrier()
+"""
+
+
+@pytest.mark.timeout(300)
+def test_bench_sharded_setup_under_torchrun(tmp_path):
+    """bench.py's N > 1 setup wiring (refined unit cube, 64 -> here 8 subdomains per rank, gloo exchange), 4 ranks on the CPU."""
+    import socket
+
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        port = s.getsockname()[1]
+    script = tmp_path / "bench_worker.py"
+    script.write_text(BENCH_WORKER.format(root=os.path.dirname(HERE)))
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=4", "--master-addr", "127.0.0.1",
+                        "--master-port", str(port), str(script)], capture_output=True, text=True, timeout=280)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-3000:]
