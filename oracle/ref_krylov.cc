@@ -39,7 +39,9 @@ struct OracleProblem {
   std::vector<const std::int64_t *> pi, px;
   std::vector<const double *> x;
   std::vector<std::int64_t> z_ptr;
-  std::vector<double> chol;
+  std::vector<double> chol, a0lu;
+  std::vector<const double *> xu;  // LU packs: panels of U^T per subdomain
+  std::vector<std::int32_t> a0piv;
   int nthreads;
 
   OracleProblem(const DdmPack &pack, int nt) : p(pack), nthreads(nt)
@@ -62,6 +64,7 @@ struct OracleProblem {
       s.push_back(p[f + "s"].as<std::int32_t>());
       x.push_back(p[f + "x"].as<double>());
       perm.push_back(p[f + "perm"].as<std::int32_t>());
+      if (p.has(f + "xu")) xu.push_back(p[f + "xu"].as<double>());
       k_off[i + 1] = k_off[i] + k[i];
       z_ptr[i + 1] = z_ptr[i] + (std::int64_t)k[i] * (S.sub_ptr[i + 1] - S.sub_ptr[i]);
     }
@@ -78,6 +81,29 @@ struct OracleProblem {
     const int N0 = k_off[ns];
     chol.assign((std::size_t)std::max(1, N0) * std::max(1, N0), 0.0);
     const double *A0 = p["A0"].as<double>();
+    if ((int)xu.size() == ns && ns > 0) {
+      // non-symmetric problem: LU subdomain factors and a dense LU with row swaps of A0 (LAPACK getrf layout, row-major)
+      S.xu = xu.data();
+      a0lu.assign(A0, A0 + (std::size_t)N0 * N0);
+      a0piv.assign(std::max(1, N0), 0);
+      for (int k = 0; k < N0; ++k) {
+        int piv = k;
+        for (int i = k + 1; i < N0; ++i)
+          if (std::fabs(a0lu[(std::size_t)i * N0 + k]) > std::fabs(a0lu[(std::size_t)piv * N0 + k])) piv = i;
+        a0piv[k] = piv;
+        if (piv != k)
+          for (int j = 0; j < N0; ++j) std::swap(a0lu[(std::size_t)k * N0 + j], a0lu[(std::size_t)piv * N0 + j]);
+        for (int i = k + 1; i < N0; ++i) {
+          const double l = a0lu[(std::size_t)i * N0 + k] / a0lu[(std::size_t)k * N0 + k];
+          a0lu[(std::size_t)i * N0 + k] = l;
+          for (int j = k + 1; j < N0; ++j) a0lu[(std::size_t)i * N0 + j] -= l * a0lu[(std::size_t)k * N0 + j];
+        }
+      }
+      if (N0 > 0) {
+        S.A0lu = a0lu.data();
+        S.A0piv = a0piv.data();
+      }
+    } else
     for (int i = 0; i < N0; ++i) // dense Cholesky, row-major lower
       for (int j = 0; j <= i; ++j) {
         double acc = A0[(std::size_t)i * N0 + j];

@@ -87,3 +87,26 @@ def test_dune_gmres_drives_the_gpu_path(packed, tmp_path, arm):
     rg, xg = run(arm, path, "gmres", str(tmp_path / "xg.bin"), typ="restricted", mode="multiplicative")
     assert rg["converged"] and abs(rg["iterations"] - rc["iterations"]) <= 1
     assert np.linalg.norm(xg - xc) <= 1e-6 * np.linalg.norm(xc)
+
+
+@needs_bin
+def test_oracle_gmres_is_dune_gmres_on_the_nonsymmetric_problem(cd_dg, tmp_path):
+    """Config C4 (LU subdomain factors, non-symmetric A0): the oracle's GMRES loop against Dune::RestartedGMResSolver
+    (solvers.hh:880-1080) on the same CPU preconditioner -- same iteration count, same defect history, same solution."""
+    from ddm_b200.setup import pack
+    from oracle import oracle
+
+    path = str(tmp_path / "cd.ddmpack")
+    pack.save_products(path, cd_dg)
+    O = oracle.Oracle(cd_dg, nthreads=2)
+    assert O.nonsym
+    x, it, conv, hist = O.gmres(cd_dg.b, reduction=1e-8, restart=30, maxit=300, restricted=True)
+    r, xd = run("cpu", path, "gmres", str(tmp_path / "x.bin"), typ="restricted")
+    assert r["converged"] and conv and r["iterations"] == it
+    # the recorded norm() calls of GMRES are the Arnoldi norms h_{j+1,j}, not defects: compare the first one (the initial
+    # preconditioned defect) and the final reduction the solver reports from its Givens recurrence
+    assert abs(r["norms"][0] - hist[0]) <= 1e-9 * hist[0]  # two dense LUs of A0 (here: LAPACK, there: a plain loop), cond(A0) eps apart
+    assert abs(r["reduction"] - hist[it] / hist[0]) <= 1e-6 * r["reduction"]
+    assert np.linalg.norm(xd - x) <= 1e-8 * np.linalg.norm(x)
+    # stopping is on the preconditioned defect; with the 1e7 coefficient jump the true defect follows three digits behind
+    assert np.linalg.norm(cd_dg.b - cd_dg.A @ xd) <= 1e-3 * np.linalg.norm(cd_dg.b)
