@@ -24,18 +24,28 @@ def rcb_partition(points, nparts):
     available; ties are broken by index so the result is deterministic.
     """
     part = np.zeros(points.shape[0], dtype=np.int32)
+    cols = [np.ascontiguousarray(points[:, d]) for d in range(points.shape[1])]
 
-    def rec(idx, p0, np_):
+    def rec(idx, p0, np_):  # idx ascending
         if np_ == 1:
             part[idx] = p0
             return
         nl = np_ // 2
-        pts = points[idx]
-        ax = int(np.argmax(pts.max(0) - pts.min(0)))
-        order = np.lexsort((idx, pts[:, ax]))
+        vs = [c[idx] for c in cols]
+        ax = int(np.argmax([x.max() - x.min() for x in vs]))
         cut = (idx.size * nl) // np_
-        rec(idx[order[:cut]], p0, nl)
-        rec(idx[order[cut:]], p0 + nl, np_ - nl)
+        # the `cut` smallest under the order (coordinate, index), by selection instead of a full sort: everything below the
+        # cut value goes left, entries equal to it go left in index order until the count is reached
+        v = vs[ax]
+        if cut == 0:
+            left = np.zeros(idx.size, dtype=bool)
+        else:
+            kth = np.partition(v, cut - 1)[cut - 1]
+            left = v < kth
+            eq = np.flatnonzero(v == kth)
+            left[eq[: cut - int(left.sum())]] = True
+        rec(idx[left], p0, nl)
+        rec(idx[~left], p0 + nl, np_ - nl)
 
     rec(np.arange(points.shape[0]), 0, nparts)
     return part

@@ -19,7 +19,7 @@ def kappa_islands(x):
     `x` is (m, d); for d = 3 the 2-D pattern is evaluated on (x, y) and the
     checkerboard also alternates in z.
     """
-    X, Y = x[:, 0], x[:, 1]
+    X, Y = np.ascontiguousarray(x[:, 0]), np.ascontiguousarray(x[:, 1])
     k = np.ones(x.shape[0])
     m = (X > 0.3) & (X < 0.9) & (Y > 0.6 - (X - 0.3) / 6) & (Y < 0.8 - (X - 0.3) / 6)
     k[m] = 1e5 * (X[m] + Y[m]) * 10.0
@@ -52,17 +52,40 @@ def kappa_channels(x, contrast=1e6):
 
 # ----------------------------------------------------------------------------- element matrices
 def p1_element_matrices(coords, cells, kappa):
-    """Stiffness matrices kappa * int grad phi_i . grad phi_j for simplices; (m, d+1, d+1)."""
+    """Stiffness matrices kappa * int grad phi_i . grad phi_j for simplices; (m, d+1, d+1).
+
+    Gradients from the closed-form inverse of the edge matrix (cofactors), component arrays over all elements at once: no
+    per-element LAPACK call, no small batched products."""
     d = coords.shape[1]
-    v = coords[cells]  # (m, d+1, d)
-    J = v[:, 1:, :] - v[:, :1, :]  # rows = edge vectors
-    det = np.linalg.det(J)
-    vol = np.abs(det) / {2: 2.0, 3: 6.0}[d]
-    Jinv = np.linalg.inv(J)  # (m, d, d); columns are gradients of phi_1..phi_d
-    G = np.empty((cells.shape[0], d + 1, d))
-    G[:, 1:, :] = np.transpose(Jinv, (0, 2, 1))
-    G[:, 0, :] = -G[:, 1:, :].sum(axis=1)
-    return (kappa * vol)[:, None, None] * np.einsum("mid,mjd->mij", G, G)
+    m = cells.shape[0]
+    if d not in (2, 3):
+        raise ValueError("p1_element_matrices: d must be 2 or 3")
+    X = [np.ascontiguousarray(coords[:, k]) for k in range(d)]
+    V = [[X[k][cells[:, j]] for k in range(d)] for j in range(d + 1)]  # V[j][k]: component k of vertex j
+    e = [[V[j][k] - V[0][k] for k in range(d)] for j in range(1, d + 1)]  # edge vectors
+    if d == 2:
+        (a, b) = e
+        det = a[0] * b[1] - a[1] * b[0]
+        g = [None, [b[1] / det, -b[0] / det], [-a[1] / det, a[0] / det]]
+    else:
+        (a, b, c) = e
+        cross = lambda u, w: [u[1] * w[2] - u[2] * w[1], u[2] * w[0] - u[0] * w[2], u[0] * w[1] - u[1] * w[0]]
+        bc, ca, ab = cross(b, c), cross(c, a), cross(a, b)
+        det = a[0] * bc[0] + a[1] * bc[1] + a[2] * bc[2]
+        g = [None, [x / det for x in bc], [x / det for x in ca], [x / det for x in ab]]
+    g[0] = [-sum(g[j][k] for j in range(1, d + 1)) for k in range(d)]  # gradients sum to zero
+    scale = kappa * (np.abs(det) / {2: 2.0, 3: 6.0}[d])
+    Ke = np.empty((m, d + 1, d + 1))
+    for i in range(d + 1):
+        for j in range(i, d + 1):
+            v = g[i][0] * g[j][0]
+            for k in range(1, d):
+                v = v + g[i][k] * g[j][k]
+            v *= scale
+            Ke[:, i, j] = v
+            if j != i:
+                Ke[:, j, i] = v
+    return Ke
 
 
 def _q1_reference_matrix():

@@ -216,8 +216,20 @@ def build(coords, cells, Ke, dirichlet, rhs, cell_part, nsub, overlap=2, pou_kin
 # ----------------------------------------------------------------------------- named configurations
 def poisson_simplex(coords, cells, nsub, kappa_fn=fem.kappa_islands, xmax=1.0, **kw):
     """P1 Poisson with Dirichlet data g = 1 - x/xmax on x in {0, xmax} (poisson_coefficient.lua:1-3,38-44)."""
+    import time
+
+    verbose, t0 = bool(os.environ.get("DDM_SETUP_VERBOSE")), [time.time()]
+
+    def tick(what):
+        if verbose:
+            print(f"[setup] {what}: {time.time() - t0[0]:.2f}s", flush=True)
+        t0[0] = time.time()
+
     d = coords.shape[1]
-    cent = coords[cells].mean(axis=1)
+    cent = coords[cells[:, 0]]  # centroids vertex by vertex: same sums as coords[cells].mean(axis=1) without the (m, d+1, d) temporary
+    for k in range(1, cells.shape[1]):
+        cent = cent + coords[cells[:, k]]
+    cent = cent / cells.shape[1]
     kap = kappa_fn(cent)
 
     def ke_fn(idx):
@@ -225,6 +237,7 @@ def poisson_simplex(coords, cells, nsub, kappa_fn=fem.kappa_islands, xmax=1.0, *
 
     dirichlet = (coords[:, 0] < 1e-6) | (coords[:, 0] > xmax - 1e-6)
     n = coords.shape[0]
+    tick("coefficient")
     part_of = kw.pop("assemble_part", None)
     if part_of is not None and kw.get("gather") is not None:
         # several processes: each assembles its slice of the cells, the partial matrices are exchanged and summed in rank order
@@ -242,7 +255,9 @@ def poisson_simplex(coords, cells, nsub, kappa_fn=fem.kappa_islands, xmax=1.0, *
     # residual at the Dirichlet lift x0 (g on the boundary, 0 inside): d = A_full x0 - f, f = 0
     x0 = np.where(dirichlet, 1.0 - coords[:, 0] / xmax, 0.0)
     rhs = A_full @ x0
+    tick("assemble A_full")
     part = decomp.rcb_partition(cent, nsub)
+    tick("partition")
     meta = dict(kw.pop("meta", {}), problem="poisson-p1", dim=d)
     return build(coords, cells, None, dirichlet, rhs, part, nsub, meta=meta, A_full=A_full, ke_fn=ke_fn, **kw)
 
