@@ -141,17 +141,53 @@ def nested_dissection(A, coords=None, leaf_size=32):
 
 
 # ----------------------------------------------------------------------------- symbolic + numeric
-def cholesky_supernodal(A, coords=None, leaf_size=32):
-    """Supernodal LL^T of SPD A; one supernode per dissection-tree node."""
-    n = A.shape[0]
-    perm, first = nested_dissection(A, coords, leaf_size)
-    nsuper = first.size - 1
-    Ap = A.tocsr()[perm][:, perm].tocsr()
-    Ap.sort_indices()
-    indptr, indices, data = Ap.indptr, Ap.indices, Ap.data
-    col2super = np.repeat(np.arange(nsuper), np.diff(first))
+def _extend_add(F, p, U):
+    """F[p, p] += U for ascending positions p.  A child's rows land in a few contiguous stretches of the parent's front, so
+    the update is added stretch by stretch with plain slices (one addition per entry either way: same result as the indexed
+    form, without its index arrays)."""
+    if p.size == 0:
+        return
+    cuts = np.flatnonzero(np.diff(p) != 1) + 1
+    if cuts.size > 24:
+        F[np.ix_(p, p)] += U
+        return
+    lo = np.concatenate(([0], cuts))
+    hi = np.concatenate((cuts, [p.size]))
+    for a0, a1 in zip(lo, hi):
+        r0 = p[a0]
+        for b0, b1 in zip(lo, hi):
+            c0 = p[b0]
+            F[r0 : r0 + (a1 - a0), c0 : c0 + (b1 - b0)] += U[a0:a1, b0:b1]
 
-    # symbolic: struct(J) = (adj(J) u children's struct) \ {<= last column of J}
+
+@dataclass
+class Analysis:
+    """Symbolic part of a factorisation -- ordering, supernodes, row structures, the permuted pattern and where each of its
+    values comes from in the caller's CSR data array.  Valid for every matrix with the same pattern: the numeric phases below
+    take only new values (cholmod_analyze / cholmod_factorize, umfpack_symbolic / umfpack_numeric; the reference's update
+    branch re-factorises with unchanged index sets, twolevel_schwarz.hh:99-104)."""
+
+    n: int
+    symmetric: bool
+    perm: np.ndarray
+    first: np.ndarray
+    structs: list
+    parent: np.ndarray
+    pending: list
+    pi: np.ndarray
+    px: np.ndarray
+    indptr: np.ndarray  # CSR of P A P^T (pattern of A + A^T for LU is only used for the structures)
+    indices: np.ndarray
+    src: np.ndarray  # (P A P^T).data = A.data[src]
+    c_indptr: np.ndarray | None = None  # LU: CSC of P A P^T
+    c_indices: np.ndarray | None = None
+    c_src: np.ndarray | None = None
+
+
+def _structures(first, indptr, indices):
+    """struct(J) = (adj(J) u children's struct) \\ {<= last column of J}; parent = supernode of the first row below."""
+    nsuper = first.size - 1
+    col2super = np.repeat(np.arange(nsuper), np.diff(first))
     structs: list[np.ndarray] = [None] * nsuper  # type: ignore
     parent = np.full(nsuper, -1, dtype=np.int64)
     pending: list[list[int]] = [[] for _ in range(nsuper)]
@@ -166,15 +202,49 @@ def cholesky_supernodal(A, coords=None, leaf_size=32):
         if st.size:
             parent[J] = col2super[st[0]]
             pending[parent[J]].append(J)
-
     ncol = np.diff(first)
     nrow = ncol + np.array([s.size for s in structs], dtype=np.int64)
     pi = np.concatenate(([0], np.cumsum(nrow))).astype(np.int64)
     px = np.concatenate(([0], np.cumsum(nrow * ncol))).astype(np.int64)
+    return structs, parent, pending, pi, px
+
+
+def analyse(A, coords=None, leaf_size=32, symmetric=True):
+    """Ordering and symbolic factorisation of the pattern of A (CSR, as stored: explicit zeros count)."""
+    A = A.tocsr()
+    n = A.shape[0]
+    tag = sp.csr_matrix((np.arange(1, A.nnz + 1, dtype=np.float64), A.indices, A.indptr), shape=A.shape)  # entry k carries k + 1
+    if symmetric:
+        perm, first = nested_dissection(A, coords, leaf_size)
+    else:
+        Pat = sp.csr_matrix((np.ones(A.nnz), A.indices, A.indptr), shape=A.shape)  # stored entries, explicit zeros included
+        S = (Pat + Pat.T).tocsr()
+        perm, first = nested_dissection(S, coords, leaf_size)
+    Tp = tag[perm][:, perm].tocsr()
+    Tp.sort_indices()
+    src = np.rint(Tp.data).astype(np.int64) - 1
+    if symmetric:
+        structs, parent, pending, pi, px = _structures(first, Tp.indptr, Tp.indices)
+        return Analysis(n=n, symmetric=True, perm=perm, first=first, structs=structs, parent=parent, pending=pending, pi=pi, px=px,
+                        indptr=Tp.indptr, indices=Tp.indices, src=src)
+    Sp = S[perm][:, perm].tocsr()
+    Sp.sort_indices()
+    structs, parent, pending, pi, px = _structures(first, Sp.indptr, Sp.indices)
+    Tc = Tp.tocsc()
+    Tc.sort_indices()
+    return Analysis(n=n, symmetric=False, perm=perm, first=first, structs=structs, parent=parent, pending=pending, pi=pi, px=px,
+                    indptr=Tp.indptr, indices=Tp.indices, src=src, c_indptr=Tc.indptr, c_indices=Tc.indices,
+                    c_src=np.rint(Tc.data).astype(np.int64) - 1)
+
+
+def numeric_cholesky(an: Analysis, values):
+    """Multifrontal LL^T with the structures of `an`; values = the matrix's CSR data array (same pattern as analysed)."""
+    n, first, structs, parent, pending, pi, px = an.n, an.first, an.structs, an.parent, an.pending, an.pi, an.px
+    nsuper = first.size - 1
+    indptr, indices = an.indptr, an.indices
+    data = np.asarray(values, dtype=np.float64)[an.src]
     s = np.empty(pi[-1], dtype=np.int32)
     x = np.empty(px[-1], dtype=np.float64)
-
-    # numeric: multifrontal
     loc = np.zeros(n, dtype=np.int64)
     updates: dict[int, np.ndarray] = {}
     for J in range(nsuper):
@@ -192,9 +262,7 @@ def cholesky_supernodal(A, coords=None, leaf_size=32):
         keep = cols >= f
         F[loc[cols[keep]], rows[keep]] = data[lo:hi][keep]
         for ch in pending[J]:
-            U = updates.pop(ch)
-            p = loc[structs[ch]]
-            F[np.ix_(p, p)] += U
+            _extend_add(F, loc[structs[ch]], updates.pop(ch))
         try:
             L11 = np.linalg.cholesky(F[:c, :c])
         except np.linalg.LinAlgError as e:
@@ -208,15 +276,13 @@ def cholesky_supernodal(A, coords=None, leaf_size=32):
             if parent[J] >= 0:
                 updates[J] = F[c:, c:] - L21 @ L21.T
         x[px[J] : px[J + 1]] = panel.ravel(order="F")
-    return SupernodalFactor(
-        n=n,
-        perm=perm.astype(np.int32),
-        super_=first.astype(np.int32),
-        pi=pi,
-        px=px,
-        s=s,
-        x=x,
-    )
+    return SupernodalFactor(n=n, perm=an.perm.astype(np.int32), super_=first.astype(np.int32), pi=pi, px=px, s=s, x=x)
+
+
+def cholesky_supernodal(A, coords=None, leaf_size=32):
+    """Supernodal LL^T of SPD A; one supernode per dissection-tree node."""
+    A = A.tocsr()
+    return numeric_cholesky(analyse(A, coords, leaf_size, symmetric=True), A.data)
 
 
 def solve_supernodal(F: SupernodalFactor, b):
@@ -301,47 +367,13 @@ def _lu_nopivot(F11):
     return L, U
 
 
-def lu_supernodal(A, coords=None, leaf_size=32):
-    """Multifrontal LU of a square matrix on the nested-dissection tree of the pattern of A + A^T.
-
-    The reference factors non-symmetric subdomain matrices with UMFPACK through Dune::UMFPack
-    (/root/reference/dune/ddm/schwarz.hh:85-92, extern/dune-istl/dune/istl/umfpack.hh); UMFPACK is absent here, so the
-    factorisation is restated (same unsymmetric-multifrontal family; pivots stay inside a front's diagonal, which is safe
-    for the diffusion-dominated DG matrices this path is used for).
-    """
-    n = A.shape[0]
-    Ac0 = A.tocsr()
-    Pat = sp.csr_matrix((np.ones(Ac0.nnz), Ac0.indices, Ac0.indptr), shape=Ac0.shape)  # stored entries, explicit zeros included
-    S = (Pat + Pat.T).tocsr()
-    perm, first = nested_dissection(S, coords, leaf_size)
+def numeric_lu(an: Analysis, values):
+    """Multifrontal LU (no pivoting across supernodes) with the structures of `an`; values = the matrix's CSR data array."""
+    n, first, structs, parent, pending, pi, px = an.n, an.first, an.structs, an.parent, an.pending, an.pi, an.px
     nsuper = first.size - 1
-    Ap = A.tocsr()[perm][:, perm]
-    Sp = S[perm][:, perm].tocsr()
-    Sp.sort_indices()
-    Ac = Ap.tocsc()  # columns of A: U^T panels are gathered from the rows, L panels from the columns
-    Ac.sort_indices()
-    Ar = Ap.tocsr()
-    Ar.sort_indices()
-    indptr, indices = Sp.indptr, Sp.indices
-    col2super = np.repeat(np.arange(nsuper), np.diff(first))
-    structs: list[np.ndarray] = [None] * nsuper  # type: ignore
-    parent = np.full(nsuper, -1, dtype=np.int64)
-    pending: list[list[int]] = [[] for _ in range(nsuper)]
-    for J in range(nsuper):
-        f, l = first[J], first[J + 1]
-        pieces = [indices[indptr[f] : indptr[l]]]
-        for c in pending[J]:
-            pieces.append(structs[c])
-        allidx = np.concatenate(pieces)
-        st = np.unique(allidx[allidx >= l])
-        structs[J] = st
-        if st.size:
-            parent[J] = col2super[st[0]]
-            pending[parent[J]].append(J)
-    ncol = np.diff(first)
-    nrow = ncol + np.array([s.size for s in structs], dtype=np.int64)
-    pi = np.concatenate(([0], np.cumsum(nrow))).astype(np.int64)
-    px = np.concatenate(([0], np.cumsum(nrow * ncol))).astype(np.int64)
+    values = np.asarray(values, dtype=np.float64)
+    r_indptr, r_indices, r_data = an.indptr, an.indices, values[an.src]  # rows of P A P^T: U^T panels
+    c_indptr, c_indices, c_data = an.c_indptr, an.c_indices, values[an.c_src]  # columns: L panels
     s = np.empty(pi[-1], dtype=np.int32)
     x = np.empty(px[-1], dtype=np.float64)
     xu = np.empty(px[-1], dtype=np.float64)
@@ -356,21 +388,19 @@ def lu_supernodal(A, coords=None, leaf_size=32):
         s[pi[J] : pi[J + 1]] = idx
         loc[idx] = np.arange(m)
         F = np.zeros((m, m))
-        # columns f..l-1 of A (rows >= f) and rows f..l-1 of A (columns >= f)
-        lo, hi = Ac.indptr[f], Ac.indptr[l]
-        rows = Ac.indices[lo:hi]
-        cols = np.repeat(np.arange(c), np.diff(Ac.indptr[f : l + 1]))
+        # columns f..l-1 of A (rows >= f) and rows f..l-1 of A (columns >= l)
+        lo, hi = c_indptr[f], c_indptr[l]
+        rows = c_indices[lo:hi]
+        cols = np.repeat(np.arange(c), np.diff(c_indptr[f : l + 1]))
         keep = rows >= f
-        F[loc[rows[keep]], cols[keep]] = Ac.data[lo:hi][keep]
-        lo, hi = Ar.indptr[f], Ar.indptr[l]
-        cols2 = Ar.indices[lo:hi]
-        rows2 = np.repeat(np.arange(c), np.diff(Ar.indptr[f : l + 1]))
+        F[loc[rows[keep]], cols[keep]] = c_data[lo:hi][keep]
+        lo, hi = r_indptr[f], r_indptr[l]
+        cols2 = r_indices[lo:hi]
+        rows2 = np.repeat(np.arange(c), np.diff(r_indptr[f : l + 1]))
         keep = cols2 >= l
-        F[rows2[keep], loc[cols2[keep]]] = Ar.data[lo:hi][keep]
+        F[rows2[keep], loc[cols2[keep]]] = r_data[lo:hi][keep]
         for ch in pending[J]:
-            U = updates.pop(ch)
-            p = loc[structs[ch]]
-            F[np.ix_(p, p)] += U
+            _extend_add(F, loc[structs[ch]], updates.pop(ch))
         L11, U11 = _lu_nopivot(F[:c, :c])
         pl = np.empty((m, c), order="F")
         pu = np.empty((m, c), order="F")
@@ -385,7 +415,19 @@ def lu_supernodal(A, coords=None, leaf_size=32):
                 updates[J] = F[c:, c:] - L21 @ U12
         x[px[J] : px[J + 1]] = pl.ravel(order="F")
         xu[px[J] : px[J + 1]] = pu.ravel(order="F")
-    return SupernodalLU(n=n, perm=perm.astype(np.int32), super_=first.astype(np.int32), pi=pi, px=px, s=s, x=x, xu=xu)
+    return SupernodalLU(n=n, perm=an.perm.astype(np.int32), super_=first.astype(np.int32), pi=pi, px=px, s=s, x=x, xu=xu)
+
+
+def lu_supernodal(A, coords=None, leaf_size=32):
+    """Multifrontal LU of a square matrix on the nested-dissection tree of the pattern of A + A^T.
+
+    The reference factors non-symmetric subdomain matrices with UMFPACK through Dune::UMFPack
+    (/root/reference/dune/ddm/schwarz.hh:85-92, extern/dune-istl/dune/istl/umfpack.hh); UMFPACK is absent here, so the
+    factorisation is restated (same unsymmetric-multifrontal family; pivots stay inside a front's diagonal, which is safe
+    for the diffusion-dominated DG matrices this path is used for).
+    """
+    A = A.tocsr()
+    return numeric_lu(analyse(A, coords, leaf_size, symmetric=False), A.data)
 
 
 def solve_supernodal_lu(F: SupernodalLU, b):

@@ -6,7 +6,7 @@ pdelab_helper.hh:44-82), overlap growth, partition of unity, the POU coarse spac
 (twolevel_schwarz.hh:47-51,107), subdomain factorisation, upload; the Galerkin matrix is assembled on the GPU
 (ddm_galerkin_assemble).  Every later apply() with a matrix of the same pattern only refreshes values
 (twolevel_schwarz.hh:99-104): operator values, numeric re-factorisation into the existing device tiles, coarse matrix -- index
-sets, bases, schedules and device allocations are kept.  Solver and preconditioner options follow the reference's
+sets, orderings and symbolic factorisations, bases, schedules and device allocations are kept.  Solver and preconditioner options follow the reference's
 ParameterTree keys (overlap, mode, fine.type, solver.type/restart/maxit; defaults :117-123: GMRES(30), maxit 1000).
 One GPU per solver object.
 """
@@ -29,14 +29,24 @@ _G: dict = {}
 
 
 def _factor_job(i):
+    """First call: extract A_i = R_i A R_i^T, analyse its pattern, factor.  Later calls (pattern unchanged): numeric phase only,
+    on the values picked straight out of the new operator's data array."""
     from threadpoolctl import threadpool_limits
 
     with threadpool_limits(1):
+        A, sym = _G["A"], _G["symmetric"]
+        numeric = factor.numeric_cholesky if sym else factor.numeric_lu
+        if _G["analysis"] is not None:
+            an, src = _G["analysis"][i], _G["src"][i]
+            return i, numeric(an, A.data[src]), None, None
         s = _G["subs"][i]
-        Ai = _G["A"][s][:, s].tocsr()
-        Ai.sort_indices()
-        fn = factor.cholesky_supernodal if _G["symmetric"] else factor.lu_supernodal
-        return i, fn(Ai, _G["coords"][s], 32)
+        tag = sp.csr_matrix((np.arange(1, A.nnz + 1, dtype=np.float64), A.indices, A.indptr), shape=A.shape)
+        Ti = tag[s][:, s].tocsr()
+        Ti.sort_indices()
+        src = np.rint(Ti.data).astype(np.int64) - 1  # A_i.data = A.data[src]
+        Ai = sp.csr_matrix((A.data[src], Ti.indices, Ti.indptr), shape=Ti.shape)
+        an = factor.analyse(Ai, _G["coords"][s], 32, symmetric=sym)
+        return i, numeric(an, Ai.data), an, src
 
 
 class TwoLevelSchwarzSolver:
@@ -55,20 +65,31 @@ class TwoLevelSchwarzSolver:
         self.P = None
         self.res = None
         self.updates = 0
+        self._analysis = None  # per subdomain: factor.Analysis, kept across value updates (twolevel_schwarz.hh:99-104)
+        self._src = None  # per subdomain: positions of A_i's values in the operator's data array
 
     # -- setup pieces
     def _factors(self, A):
+        first = self._analysis is None
         _G.clear()
-        _G.update(A=A, subs=self.P.subs if self.P else self._subs, coords=self.coords, symmetric=self.symmetric)
+        _G.update(A=A, subs=self.P.subs if self.P else self._subs, coords=self.coords, symmetric=self.symmetric,
+                  analysis=self._analysis, src=self._src)
         out = [None] * self.nsub
+        ans, srcs = [None] * self.nsub, [None] * self.nsub
+
+        def keep(i, F, an, src):
+            out[i], ans[i], srcs[i] = F, an, src
+
         if self.workers > 1:
             with mp.get_context("fork").Pool(self.workers) as pool:
-                for i, F in pool.imap_unordered(_factor_job, range(self.nsub)):
-                    out[i] = F
+                for res in pool.imap_unordered(_factor_job, range(self.nsub)):
+                    keep(*res)
         else:
             for i in range(self.nsub):
-                out[i] = _factor_job(i)[1]
+                keep(*_factor_job(i))
         _G.clear()
+        if first:
+            self._analysis, self._src = ans, srcs
         return out
 
     def _first(self, A, b):
