@@ -124,14 +124,39 @@ def assemble(n, cells, Ke, subset=None):
     return A
 
 
-def assemble_chunked(n, cells, ke_fn, chunk=4_000_000):
+_ASM: dict = {}
+
+
+def _assemble_chunk(lo):
+    n, cells, ke_fn, chunk = _ASM["n"], _ASM["cells"], _ASM["ke_fn"], _ASM["chunk"]
+    idx = np.arange(lo, min(lo + chunk, cells.shape[0]))
+    return assemble(n, cells[idx], ke_fn(idx))
+
+
+def assemble_chunked(n, cells, ke_fn, chunk=4_000_000, workers=1):
     """assemble() over chunks of cells, element matrices produced on the fly by ke_fn(index array): bounds the transient
-    memory of large meshes (several ranks build the same global matrix side by side)."""
-    A = None
-    for lo in range(0, cells.shape[0], chunk):
-        idx = np.arange(lo, min(lo + chunk, cells.shape[0]))
-        part = assemble(n, cells[idx], ke_fn(idx))
-        A = part if A is None else A + part
+    memory of large meshes (several ranks build the same global matrix side by side).  workers > 1: the chunks are assembled
+    by forked processes and summed in chunk order, so the result does not depend on the worker count."""
+    starts = list(range(0, cells.shape[0], chunk))
+    _ASM.update(n=n, cells=cells, ke_fn=ke_fn, chunk=chunk)
+    try:
+        if workers > 1 and len(starts) > 1:
+            import multiprocessing as mp
+
+            with mp.get_context("fork").Pool(min(workers, len(starts))) as pool:
+                parts = pool.imap(_assemble_chunk, starts)
+                A = None
+                for part in parts:
+                    A = part if A is None else A + part
+        else:
+            A = None
+            for lo in starts:
+                part = _assemble_chunk(lo)
+                A = part if A is None else A + part
+    finally:
+        _ASM.clear()
+    if A is None:
+        A = sp.csr_matrix((n, n))
     A = A.tocsr()
     A.sum_duplicates()
     A.sort_indices()

@@ -251,7 +251,8 @@ def poisson_simplex(coords, cells, nsub, kappa_fn=fem.kappa_islands, xmax=1.0, *
         A_full.sum_duplicates()
         A_full.sort_indices()
     else:
-        A_full = fem.assemble_chunked(n, cells, ke_fn)  # element matrices are produced chunk by chunk, never all at once
+        # element matrices are produced chunk by chunk, never all at once; one process: chunks in parallel
+        A_full = fem.assemble_chunked(n, cells, ke_fn, workers=kw.get("workers") or (os.cpu_count() or 1))
     # residual at the Dirichlet lift x0 (g on the boundary, 0 inside): d = A_full x0 - f, f = 0
     x0 = np.where(dirichlet, 1.0 - coords[:, 0] / xmax, 0.0)
     rhs = A_full @ x0
