@@ -204,7 +204,9 @@ def build(coords, cells, Ke, dirichlet, rhs, cell_part, nsub, overlap=2, pou_kin
         for part in gather({i: Z[i] for i in todo}):
             for i, Zi in part.items():
                 Z[i] = Zi
-        A0 = np.hstack(gather(coarse_mod.galerkin_columns(A, subs, Z, todo)))
+        # column blocks travel sparse: only the neighbour blocks are non-zero (a few percent of N0 x k at hundreds of subdomains)
+        mine_cols = sp.csr_matrix(coarse_mod.galerkin_columns(A, subs, Z, todo))
+        A0 = np.hstack([blk.toarray() for blk in gather(mine_cols)])
     tick("galerkin")
     m = dict(meta or {})
     m.update(nsub=nsub, overlap=overlap, pou=pou_kind, coarse=coarse, nev=nev, n=int(n), N0=int(A0.shape[0]), symmetric=bool(symmetric))
