@@ -266,18 +266,30 @@ def poisson_simplex(coords, cells, nsub, kappa_fn=fem.kappa_islands, xmax=1.0, *
 
 
 def poisson_q1_cube(ncell, pgrid, kappa_fn=fem.kappa_channels, **kw):
-    """Structured Q1 Poisson on the unit cube, brick decomposition (config C5 family)."""
+    """Structured Q1 Poisson on the unit cube, brick decomposition (config C5 family).  Element matrices are produced chunk by
+    chunk (64 doubles per cell: 6 GB at the 231^3 cells of one C5 GPU share if held at once)."""
     shape = (ncell,) * 3
     coords, cells = mesh.structured_q1(shape)
-    cent = coords[cells].mean(axis=1)
-    Ke = fem.q1_element_matrices(1.0 / ncell, kappa_fn(cent))
+    cent = coords[cells[:, 0]]
+    for k in range(1, cells.shape[1]):
+        cent = cent + coords[cells[:, k]]
+    cent = cent / cells.shape[1]
+    kap = kappa_fn(cent)
+    del cent
+    h = 1.0 / ncell
+
+    def ke_fn(idx):
+        return fem.q1_element_matrices(h, kap[idx])
+
+    n = coords.shape[0]
     dirichlet = (coords[:, 0] < 1e-9) | (coords[:, 0] > 1.0 - 1e-9)
+    A_full = fem.assemble_chunked(n, cells, ke_fn, chunk=1_000_000, workers=kw.get("workers") or (os.cpu_count() or 1))
     x0 = np.where(dirichlet, 1.0 - coords[:, 0], 0.0)
-    rhs = fem.assemble(coords.shape[0], cells, Ke) @ x0
+    rhs = A_full @ x0
     part = decomp.box_partition(shape, pgrid)
     nsub = int(np.prod(pgrid))
     meta = dict(kw.pop("meta", {}), problem="poisson-q1", dim=3, ncell=ncell, pgrid=tuple(pgrid))
-    return build(coords, cells, Ke, dirichlet, rhs, part, nsub, meta=meta, **kw)
+    return build(coords, cells, None, dirichlet, rhs, part, nsub, meta=meta, A_full=A_full, ke_fn=ke_fn, **kw)
 
 
 def unitcube_p1(ncell, nsub, **kw):

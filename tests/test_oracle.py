@@ -136,3 +136,20 @@ def test_single_subdomain_is_a_direct_solve():
     x, it, conv, _ = O.pcg(P.b, reduction=1e-8, maxit=10, with_coarse=False)
     assert conv and it <= 2
     assert np.linalg.norm(P.b - P.A @ x) <= 1e-10 * np.linalg.norm(P.b)
+
+
+def test_q1_brick_family_converges():
+    """Config C5 family at toy size (structured Q1, channels coefficient, brick subdomains): the setup restatement gives a
+    consistent problem and the two-level method converges on it."""
+    from ddm_b200.setup import problem
+    from oracle import oracle
+
+    P = problem.poisson_q1_cube(12, (2, 2, 2), overlap=2, coarse="geneo", nev=6, workers=1)
+    assert P.n == 13 ** 3 and P.nsub == 8 and abs(P.A - P.A.T).max() <= 1e-12 * abs(P.A).max()
+    tot = np.zeros(P.n)
+    for s, d in zip(P.subs, P.pou):
+        np.add.at(tot, s, d)
+    assert np.allclose(tot, 1.0, atol=1e-12)
+    O = oracle.Oracle(P, nthreads=2)
+    x, it, conv, hist = O.pcg(P.b, reduction=1e-8, maxit=100)
+    assert conv and it < 60 and np.linalg.norm(P.b - P.A @ x) <= 1e-7 * np.linalg.norm(P.b)
