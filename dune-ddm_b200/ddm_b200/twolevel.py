@@ -149,3 +149,77 @@ class TwoLevelSchwarzSolver:
         if self.ctx is not None:
             self.ctx.close()
             self.ctx = None
+
+
+class TwoLevelSchwarzPreconditioner:
+    """The reference's one-object preconditioner (examples/pdelab_schwarz.hh:26-203): built from a problem description and a
+    parameter tree, it hides index sets, partition of unity, coarse space, both levels and their combination behind the
+    Dune::Preconditioner interface (pre / apply / post / category) and hands out the matching operator and scalar product.
+
+    problem: dict with the keys of setup.problem.build -- coords, cells, Ke (element matrices, or ke_fn), dirichlet, rhs,
+    cell_part, nsub; optional A_full, symmetric.  ptree keys (defaults as in the reference): overlap (1, pdelab_schwarz.hh:44),
+    coarsespace.type (geneo; supported here: geneo, pou, none -- the other types of :56-63 raise like Dune::NotImplemented),
+    coarse_space.nev / shift / tolerance (eigensolver_params.hh:43-51), pou.type / pou.shrink, schwarz.type (restricted,
+    schwarz.hh:80), combined_preconditioner.mode (additive, combined_preconditioner.hh:57).
+    """
+
+    category = "nonoverlapping"
+    _known = ("geneo", "pou", "none")
+    _other = ("constraint_geneo", "msgfem", "geneo_ring", "msgfem_ring", "harmonic_extension", "algebraic_geneo", "algebraic_msgfem",
+              "svd", "msgfem_euclid")
+
+    def __init__(self, problem, ptree=None, device=0, workers=None):
+        from .setup import problem as setup_problem
+
+        cfg = {"overlap": 1, "coarsespace.type": "geneo", "coarse_space.nev": 16, "coarse_space.shift": 1e-3, "coarse_space.tolerance": 1e-5,
+               "pou.type": "distance", "pou.shrink": 0, "schwarz.type": "restricted", "combined_preconditioner.mode": "additive"}
+        cfg.update(ptree or {})
+        kind = cfg["coarsespace.type"]
+        if kind not in self._known:
+            if kind in self._other:
+                raise DDMError(f"coarse space type '{kind}' is not implemented on this path")
+            raise DDMError("Unknown coarse space type: " + str(kind))  # pdelab_schwarz.hh:63
+        self.cfg = cfg
+        p = dict(problem)
+        self.P = setup_problem.build(p["coords"], p["cells"], p.get("Ke"), p["dirichlet"], p["rhs"], p["cell_part"], p["nsub"],
+                                     overlap=cfg["overlap"], pou_kind=cfg["pou.type"], shrink=cfg["pou.shrink"], coarse=kind,
+                                     nev=cfg["coarse_space.nev"], shift=cfg["coarse_space.shift"], eig_tol=cfg["coarse_space.tolerance"],
+                                     workers=workers, A_full=p.get("A_full"), symmetric=p.get("symmetric", True), ke_fn=p.get("ke_fn"))
+        has_coarse = self.P.A0.shape[0] > 0
+        self.ctx = api.Context.from_products(self.P, device=device, with_coarse=has_coarse)
+        self._op = api.NonOverlappingOperator(self.ctx)
+        self._prec = api.CombinedPreconditioner(cfg["combined_preconditioner.mode"])
+        self._prec.set_op(self._op)
+        self._prec.add(api.SchwarzPreconditioner(self.ctx, cfg["schwarz.type"]))
+        if has_coarse:
+            self._prec.add(api.GalerkinPreconditioner(self.ctx))
+
+    # Dune::Preconditioner
+    def pre(self, x, b):
+        self._prec.pre(x, b)
+
+    def apply(self, v, d):
+        self._prec.apply(v, d)
+
+    def post(self, x):
+        self._prec.post(x)
+
+    # what the reference's getters hand to the solver factory (pdelab_schwarz.hh:190-197)
+    def getNonOverlappingOperator(self):
+        return self._op
+
+    def getScalarProduct(self):
+        return api.NonOverlappingScalarProduct(self.ctx)
+
+    def get_basis(self):
+        return self.P.Z
+
+    @property
+    def combined(self):
+        """The CombinedPreconditioner inside (what the device-resident Krylov loops of api.CGSolver / RestartedGMResSolver take)."""
+        return self._prec
+
+    def close(self):
+        if self.ctx is not None:
+            self.ctx.close()
+            self.ctx = None
