@@ -414,6 +414,84 @@ class CGSolver:
         return x, InverseOperatorResult(res.iterations, bool(res.converged), res.reduction, res.conv_rate, res.elapsed, hist[: res.iterations + 1])
 
 
+class BiCGSTABSolver:
+    """Dune::BiCGSTABSolver (solvers.hh:419-590) over the same three interfaces: the literal drop-in loop, every dot and norm
+    read on the host where the reference reads it.  Iterations count in halves as in the reference (the stopping test runs
+    after each of the two corrections of a step); the reported count is truncated the way InverseOperatorResult stores it."""
+
+    EPSILON = 1e-80
+
+    def __init__(self, op, sp, prec, reduction=1e-8, maxit=100, verbose=0):
+        self.op, self.sp, self.prec = op, sp, prec
+        self.reduction, self.maxit, self.verbose = reduction, maxit, verbose
+
+    def apply(self, x, b):
+        ctx = x.ctx
+        r = b
+        self.prec.pre(x, r)
+        self.op.applyscaleadd(-1.0, x, r)  # b becomes the defect
+        rt = ctx.vector().assign(r)
+        norm = self.sp.norm(r)
+        hist = [norm]
+        def0 = norm
+
+        def step(v):
+            if not np.isfinite(v):
+                raise DDMError("BiCGSTABSolver: defect is infinite or NaN")  # SolverAbort, solver.hh:458-466
+            return v < def0 * self.reduction or v < 1e-30
+
+        it = 0.0
+        if not step(norm):
+            p, v, t, y = (ctx.vector().fill(0.0) for _ in range(4))
+            rho = alpha = omega = 1.0
+            it = 0.5
+            while it < self.maxit:
+                rho_new = self.sp.dot(rt, r)
+                if abs(rho) <= self.EPSILON:
+                    raise DDMError(f"breakdown in BiCGSTAB - rho {rho} <= EPSILON {self.EPSILON} after {it} iterations")
+                if abs(omega) <= self.EPSILON:
+                    raise DDMError(f"breakdown in BiCGSTAB - omega {omega} <= EPSILON {self.EPSILON} after {it} iterations")
+                if it < 1:
+                    p.assign(r)
+                else:
+                    beta = 0.0 if norm == 0.0 else (rho_new / rho) * (alpha / omega)
+                    p.axpy(-omega, v)
+                    p *= beta
+                    p += r
+                y.fill(0.0)
+                self.prec.apply(y, p)
+                self.op.apply(y, v)
+                h = self.sp.dot(rt, v)
+                if abs(h) < self.EPSILON:
+                    raise DDMError(f"abs(h) < EPSILON in BiCGSTAB - abs(h) {abs(h)} < EPSILON {self.EPSILON} after {it} iterations")
+                alpha = 0.0 if norm == 0.0 else rho_new / h
+                x.axpy(alpha, y)
+                r.axpy(-alpha, v)
+                norm = self.sp.norm(r)
+                hist.append(norm)
+                if step(norm):
+                    break
+                it += 0.5
+                y.fill(0.0)
+                self.prec.apply(y, r)
+                self.op.apply(y, t)
+                h = self.sp.dot(t, t)
+                omega = 0.0 if norm == 0.0 else self.sp.dot(t, r) / h
+                x.axpy(omega, y)
+                r.axpy(-omega, t)
+                rho = rho_new
+                norm = self.sp.norm(r)
+                hist.append(norm)
+                if step(norm):
+                    break
+                it += 0.5
+            else:
+                it -= 0.5  # the loop ran out: the last completed half step is what Iteration recorded
+        self.prec.post(x)
+        red = norm / def0 if def0 > 0 else 0.0
+        return InverseOperatorResult(int(it), step(norm), red, red ** (1.0 / it) if it else 0.0, 0.0, np.array(hist))
+
+
 class RestartedGMResSolver:
     """Dune::RestartedGMResSolver (solvers.hh:923-1035) over the same three interfaces.
 

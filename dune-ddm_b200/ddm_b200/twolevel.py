@@ -55,7 +55,7 @@ class TwoLevelSchwarzSolver:
         cfg = dict(overlap=1, mode="additive", **{"fine.type": "restricted", "solver.type": "restartedgmressolver",
                                                    "solver.restart": 30, "solver.maxit": 1000, "pou.type": "distance", "pou.shrink": 0})
         cfg.update(config or {})
-        if cfg["solver.type"] not in ("restartedgmressolver", "cgsolver"):
+        if cfg["solver.type"] not in ("restartedgmressolver", "cgsolver", "bicgstabsolver"):
             raise DDMError(f"Unknown solver type '{cfg['solver.type']}'")
         self.cfg, self.coords, self.cells, self.part, self.nsub = cfg, np.asarray(coords), np.asarray(dof_cells), np.asarray(cell_part), int(nsub)
         self.symmetric, self.device = bool(symmetric), device
@@ -137,10 +137,12 @@ class TwoLevelSchwarzSolver:
         prec.add(api.GalerkinPreconditioner(ctx))
         if cfg["solver.type"] == "cgsolver":
             solver = api.CGSolver(op, spr, prec, reduction=reduction, maxit=cfg["solver.maxit"])
+        elif cfg["solver.type"] == "bicgstabsolver":
+            solver = api.BiCGSTABSolver(op, spr, prec, reduction=reduction, maxit=cfg["solver.maxit"])
         else:
             solver = api.RestartedGMResSolver(op, spr, prec, reduction=reduction, restart=cfg["solver.restart"], maxit=cfg["solver.maxit"])
         x, b = ctx.vector(np.asarray(z, dtype=np.float64)), ctx.vector(np.asarray(r, dtype=np.float64))
-        self.res = solver.solve_device(x, b)
+        self.res = solver.solve_device(x, b) if hasattr(solver, "solve_device") else solver.apply(x, b)
         z[:] = x.download()
         r[:] = b.download()
         return self.res

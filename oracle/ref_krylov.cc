@@ -4,7 +4,7 @@
 //             PCG loop against the real solvers.hh and is the CPU baseline's outer loop;
 //   gpu       the product (libddm_b200.so) through dune/ddm_b200/adaptors.hh with X = DeviceVector;
 //   gpu-host  the product with X = Dune::BlockVector<FieldVector<double,1>>: the unchanged-driver drop-in.
-// Usage: dune_krylov <cpu|gpu|gpu-host> <problem.ddmpack> <cg|gmres> <reduction> <maxit> <restart>
+// Usage: dune_krylov <cpu|gpu|gpu-host> <problem.ddmpack> <cg|gmres|bicgstab> <reduction> <maxit> <restart>
 //                    <standard|restricted> <additive|multiplicative> <with_coarse 0|1> <nthreads> [solution.bin]
 // Prints one JSON line.
 #include <chrono>
@@ -178,6 +178,9 @@ static Dune::InverseOperatorResult run(const std::string &solver, std::shared_pt
   } else if (solver == "gmres") {
     Dune::RestartedGMResSolver<X> gm(op, sp, prec, reduction, restart, maxit, 0);
     gm.apply(x, b, res);
+  } else if (solver == "bicgstab") {
+    Dune::BiCGSTABSolver<X> bi(op, sp, prec, reduction, maxit, 0);
+    bi.apply(x, b, res);
   } else
     DUNE_THROW(Dune::Exception, "unknown solver " << solver);
   return res;
@@ -186,7 +189,7 @@ static Dune::InverseOperatorResult run(const std::string &solver, std::shared_pt
 int main(int argc, char **argv)
 {
   if (argc < 11) {
-    std::fprintf(stderr, "usage: %s <cpu|gpu|gpu-host> pack <cg|gmres> reduction maxit restart <standard|restricted> "
+    std::fprintf(stderr, "usage: %s <cpu|gpu|gpu-host> pack <cg|gmres|bicgstab> reduction maxit restart <standard|restricted> "
                          "<additive|multiplicative> with_coarse nthreads [solution.bin]\n", argv[0]);
     return 2;
   }

@@ -110,3 +110,150 @@ def test_oracle_gmres_is_dune_gmres_on_the_nonsymmetric_problem(cd_dg, tmp_path)
     assert np.linalg.norm(xd - x) <= 1e-8 * np.linalg.norm(x)
     # stopping is on the preconditioned defect; with the 1e7 coefficient jump the true defect follows three digits behind
     assert np.linalg.norm(cd_dg.b - cd_dg.A @ xd) <= 1e-3 * np.linalg.norm(cd_dg.b)
+
+
+@needs_bin
+@pytest.mark.parametrize("which", ["small3d", "cd_dg"])
+def test_dune_bicgstab_on_the_oracle_converges(request, tmp_path, which):
+    """The third solver the reference's factory hands out (solverfactory.hh:148-167, examples/*.ini `type = bicgstabsolver`) needs
+    nothing beyond the same three interfaces: Dune::BiCGSTABSolver on the CPU preconditioner, symmetric and non-symmetric problem."""
+    from ddm_b200.setup import pack
+
+    P = request.getfixturevalue(which)
+    path = str(tmp_path / "p.ddmpack")
+    pack.save_products(path, P)
+    r, xd = run("cpu", path, "bicgstab", str(tmp_path / "x.bin"), typ="restricted", mode="multiplicative")
+    assert r["converged"] and r["iterations"] < 60
+    assert np.linalg.norm(P.b - P.A @ xd) <= (1e-7 if which == "small3d" else 1e-3) * np.linalg.norm(P.b)
+
+
+class _HostVec:
+    """numpy stand-in for api.DeviceVector (the operations the Krylov loops use), to run api.BiCGSTABSolver without a GPU."""
+
+    def __init__(self, ctx, values=None):
+        self.ctx, self.a = ctx, np.zeros(ctx.n) if values is None else np.array(values, dtype=np.float64)
+
+    def fill(self, v):
+        self.a[:] = v
+        return self
+
+    def assign(self, o):
+        self.a[:] = o.a
+        return self
+
+    def axpy(self, s, o):
+        self.a += s * o.a
+        return self
+
+    def __imul__(self, s):
+        self.a *= s
+        return self
+
+    def __iadd__(self, o):
+        self.a += o.a
+        return self
+
+
+class _HostCtx:
+    def __init__(self, n):
+        self.n = n
+
+    def vector(self, values=None):
+        return _HostVec(self, values)
+
+
+@needs_bin
+def test_python_bicgstab_loop_is_dune_bicgstab(packed, tmp_path):
+    """api.BiCGSTABSolver restates solvers.hh:419-590; on host stand-ins for operator, scalar product and preconditioner (the
+    oracle) it must walk through the same defect norms as Dune::BiCGSTABSolver on the same CPU preconditioner."""
+    from ddm_b200 import api
+    from oracle import oracle
+
+    P, path = packed
+    O = oracle.Oracle(P, nthreads=2)
+
+    class Op:
+        def apply(self, x, y):
+            y.a[:] = P.A @ x.a
+
+        def applyscaleadd(self, alpha, x, y):
+            y.a += alpha * (P.A @ x.a)
+
+    class Sp:
+        def dot(self, x, y):
+            return float(x.a @ y.a)
+
+        def norm(self, x):
+            return float(np.sqrt(x.a @ x.a))
+
+    class Prec:
+        def pre(self, x, b):
+            pass
+
+        def post(self, x):
+            pass
+
+        def apply(self, v, d):
+            v.a[:] = O.twolevel_apply(d.a, restricted=True, mode="multiplicative")
+
+    ctx = _HostCtx(P.n)
+    x, b = ctx.vector(), ctx.vector(P.b)
+    res = api.BiCGSTABSolver(Op(), Sp(), Prec(), reduction=1e-8, maxit=300).apply(x, b)
+    r, xd = run("cpu", path, "bicgstab", str(tmp_path / "x.bin"), typ="restricted", mode="multiplicative")
+    assert res.converged and r["converged"] and res.iterations == r["iterations"]
+    h = np.array(r["norms"])
+    assert h.size == res.history.size
+    assert np.max(np.abs(h[:4] - res.history[:4]) / h[:4]) <= 1e-10 and np.max(np.abs(h - res.history) / h) <= 1e-4
+    assert np.linalg.norm(x.a - xd) <= 1e-8 * np.linalg.norm(xd)
+    # iteration cap: the count is the last half step the stopping test saw
+    x, b = ctx.vector(), ctx.vector(P.b)
+    res = api.BiCGSTABSolver(Op(), Sp(), Prec(), reduction=1e-8, maxit=2).apply(x, b)
+    r, _ = run("cpu", path, "bicgstab", str(tmp_path / "x2.bin"), maxit=2, typ="restricted", mode="multiplicative")
+    assert not res.converged and not r["converged"] and res.iterations == r["iterations"] and res.history.size == len(r["norms"])
+
+
+@needs_bin
+@pytest.mark.parametrize("solver", ["cg", "gmres"])
+def test_python_dropin_loops_are_dune_solvers(packed, tmp_path, solver):
+    """api.CGSolver.apply / api.RestartedGMResSolver.apply (the literal drop-in loops of the Python mirror) on host stand-ins
+    against Dune's solvers on the same CPU preconditioner: same iteration count, same solution."""
+    from ddm_b200 import api
+    from oracle import oracle
+
+    P, path = packed
+    O = oracle.Oracle(P, nthreads=2)
+    typ, mode = ("standard", "additive") if solver == "cg" else ("restricted", "multiplicative")
+
+    class Op:
+        def apply(self, x, y):
+            y.a[:] = P.A @ x.a
+
+        def applyscaleadd(self, alpha, x, y):
+            y.a += alpha * (P.A @ x.a)
+
+    class Sp:
+        def dot(self, x, y):
+            return float(x.a @ y.a)
+
+        def norm(self, x):
+            return float(np.sqrt(x.a @ x.a))
+
+    class Prec:
+        def pre(self, x, b):
+            pass
+
+        def post(self, x):
+            pass
+
+        def apply(self, v, d):
+            v.a[:] = O.twolevel_apply(d.a, restricted=typ == "restricted", mode=mode)
+
+    ctx = _HostCtx(P.n)
+    x, b = ctx.vector(), ctx.vector(P.b)
+    S = api.CGSolver(Op(), Sp(), Prec(), reduction=1e-8, maxit=300) if solver == "cg" else \
+        api.RestartedGMResSolver(Op(), Sp(), Prec(), reduction=1e-8, restart=30, maxit=300)
+    res = S.apply(x, b)
+    r, xd = run("cpu", path, solver, str(tmp_path / "x.bin"), typ=typ, mode=mode)
+    assert res.converged and r["converged"] and res.iterations == r["iterations"]
+    assert abs(res.reduction - r["reduction"]) <= 1e-4 * r["reduction"]
+    assert np.linalg.norm(x.a - xd) <= 1e-8 * np.linalg.norm(xd)
