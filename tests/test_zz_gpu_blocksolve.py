@@ -53,9 +53,10 @@ def test_batched_block_solve_equals_single_solves(request, name):
                 xi, di = x[off[i] : off[i + 1]], d[off[i] : off[i + 1]]
                 F = P.factors[i]
                 single = factor.solve_supernodal_lu(F, di) if hasattr(F, "xu") else factor.solve_supernodal(F, di)
-                # both are backward-stable solves of the same system: compare through the residual (independent of cond(A_i)) ...
+                # through the residual: the device sweeps multiply by explicit inverses of the diagonal blocks, so their backward
+                # error carries the conditioning of those blocks (not of A_i); a wrong solve would be O(1) here
                 scale = abs(Ai).sum(axis=1).max() * np.linalg.norm(xi) + np.linalg.norm(di)
-                assert np.linalg.norm(Ai @ xi - di) <= 1e-13 * scale
+                assert np.linalg.norm(Ai @ xi - di) <= 1e-10 * scale
                 # ... and directly, with the room conditioning gives two FP64 evaluations of one factorisation
                 tol = max(1e-12, 64 * np.finfo(float).eps * np.linalg.cond(Ai.toarray()))
                 assert np.linalg.norm(xi - single) <= tol * np.linalg.norm(single)
