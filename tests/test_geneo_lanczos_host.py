@@ -1,0 +1,50 @@
+"""The batched shift-invert Lanczos of setup/geneo_gpu.py with the device calls replaced by host stand-ins
+(tests/lanczos_standin.py): its eigenvalues must be those of the per-subdomain ARPACK runs of the host restatement, its vectors
+span the same spaces up to clusters cut by nev, and the recurrence must stop by its own convergence test."""
+import numpy as np
+import pytest
+
+
+def _eigenproblems(P, shift=1e-3):
+    """Per subdomain: C_i = D B_neu D, the Cholesky factor of A_neu + shift C_i, and ARPACK's answer."""
+    from ddm_b200.setup import coarse, factor, fem, geneo_gpu, mesh
+
+    coords, cells = mesh.structured_simplices((P.meta_ncell,) * 3)
+    cent = coords[cells].mean(axis=1)
+    Ke = fem.p1_element_matrices(coords, cells, fem.kappa_islands(cent))
+    shared = np.zeros(P.n, dtype=np.int32)
+    for s in P.subs:
+        shared[s] += 1
+    Cs, Ks, ref = [], [], []
+    for i, s in enumerate(P.subs):
+        An, Bn = coarse.neumann_matrices(P.n, cells, Ke, s, shared, P.dirichlet)
+        Cm = geneo_gpu.weighted_overlap_matrix(Bn, P.pou[i])
+        Cs.append(Cm)
+        Ks.append(factor.cholesky_supernodal((An + shift * Cm).tocsr(), coords[s], 32))
+        ref.append(coarse.geneo_basis(An, Bn, P.pou[i], P.dirichlet[s], nev=P.meta["nev"], shift=shift, tol=1e-5))
+    return Cs, Ks, ref
+
+
+@pytest.mark.parametrize("ncell,nsub,nev", [(10, 6, 5), (12, 8, 6)])
+def test_host_run_of_the_batched_lanczos(monkeypatch, ncell, nsub, nev):
+    from ddm_b200 import api
+    from ddm_b200.setup import geneo_gpu, problem
+
+    import lanczos_standin
+
+    P = problem.unitcube_p1(ncell, nsub, overlap=2, nev=nev, workers=1)
+    P.meta_ncell = ncell
+    Cs, Ks, ref = _eigenproblems(P)
+    monkeypatch.setattr(api.Context, "from_products", lanczos_standin.HostContext.from_products)
+    Z, lams = geneo_gpu.batched_geneo(Cs, Ks, P.pou, [P.dirichlet[s] for s in P.subs], nev=nev, shift=1e-3, tol=1e-5)
+    ctx = lanczos_standin.HostContext.last
+    assert ctx.lib.solves <= 160 + 2  # stopped by its convergence test, not by the step limit
+    for i in range(nsub):
+        Zr, lr = ref[i]
+        k = min(lams[i].size, lr.size)
+        assert k >= nev - 1
+        # eigenvalues to the eigensolver tolerance (the zero eigenvalue of the floating subdomains absolutely)
+        assert np.allclose(lams[i][:k], lr[:k], rtol=1e-4, atol=1e-8)
+        Qa, Qb = np.linalg.qr(Z[i][:, :k])[0], np.linalg.qr(Zr[:, :k])[0]
+        sv = np.linalg.svd(Qa.T @ Qb, compute_uv=False)
+        assert (sv > 1.0 - 1e-4).sum() >= k - 1  # one direction may differ where nev cuts a cluster
