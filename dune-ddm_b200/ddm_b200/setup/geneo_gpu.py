@@ -101,7 +101,7 @@ def batched_geneo(Cs, K_factors, pous, dirichlets, nev=16, shift=1e-3, tol=1e-5,
             # Ritz pairs per subdomain
             A_ = np.array(alphas)  # (m, ns)
             B_ = np.array(betas)
-            thetas, ys, done = [], [], True
+            thetas, ys, done, late = [], [], True, []
             for i in range(ns):
                 T = np.diag(A_[:, i]) + np.diag(B_[: m - 1, i], 1) + np.diag(B_[: m - 1, i], -1)
                 th, y = np.linalg.eigh(T)
@@ -111,9 +111,15 @@ def batched_geneo(Cs, K_factors, pous, dirichlets, nev=16, shift=1e-3, tol=1e-5,
                 res = np.abs(B_[m - 1, i] * y[m - 1, :])
                 if (res > tol * np.abs(th)).any():
                     done = False
+                    late.append(i)
                 thetas.append(th)
                 ys.append(y)
             if done or m >= mmax:
+                if not done:  # as the host path does with ArpackNoConvergence: keep the Ritz pairs reached, but say so
+                    import warnings
+
+                    warnings.warn(f"batched GenEO eigensolve: {len(late)} of {ns} subdomains did not reach tolerance {tol:g} in {m} Lanczos steps "
+                                  f"(subdomains {late[:8]}{' ...' if len(late) > 8 else ''})", RuntimeWarning, stacklevel=2)
                 break
             m = min(m + 16, mmax)
         Vh = np.stack([V[k].download() for k in range(m)], axis=1)  # (P, m)

@@ -48,3 +48,18 @@ def test_host_run_of_the_batched_lanczos(monkeypatch, ncell, nsub, nev):
         Qa, Qb = np.linalg.qr(Z[i][:, :k])[0], np.linalg.qr(Zr[:, :k])[0]
         sv = np.linalg.svd(Qa.T @ Qb, compute_uv=False)
         assert (sv > 1.0 - 1e-4).sum() >= k - 1  # one direction may differ where nev cuts a cluster
+
+
+def test_step_limit_is_reported(monkeypatch):
+    from ddm_b200 import api
+    from ddm_b200.setup import geneo_gpu, problem
+
+    import lanczos_standin
+
+    P = problem.unitcube_p1(10, 6, overlap=2, nev=5, workers=1)
+    P.meta_ncell = 10
+    Cs, Ks, _ = _eigenproblems(P)
+    monkeypatch.setattr(api.Context, "from_products", lanczos_standin.HostContext.from_products)
+    with pytest.warns(RuntimeWarning, match="did not reach tolerance"):
+        Z, lams = geneo_gpu.batched_geneo(Cs, Ks, P.pou, [P.dirichlet[s] for s in P.subs], nev=5, shift=1e-3, tol=1e-12, m0=8, mmax=8)
+    assert all(z.shape[1] <= 5 for z in Z)
