@@ -50,6 +50,8 @@ def parse():
     ap.add_argument("--cpu-seconds", type=float, default=20.0, help="budget of the cpu_baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--pack", default=None, help=".ddmpack cache of the setup products: loaded if present, else built and saved")
+    ap.add_argument("--strong", action="store_true",
+                    help="strong scaling: the N = 1 problem (ncell^3 cells, nsub subdomains in total) split over the GPUs instead of a problem that grows with N")
     ap.add_argument("--setup-only", action="store_true", help="build (and save) the setup products, then exit")
     return ap.parse_args()
 
@@ -58,15 +60,24 @@ def gpu_grid(n):
     return {1: (1, 1, 1), 2: (2, 1, 1), 4: (2, 2, 1), 8: (2, 2, 2)}.get(n) or (n, 1, 1)
 
 
+def job_shape(a, world):
+    """(cells per axis, subdomains in total): weak scaling refines the unit cube with N and hosts nsub subdomains per GPU,
+    strong scaling keeps the N = 1 problem and deals its nsub subdomains out."""
+    if a.strong:
+        if a.nsub % world:
+            raise SystemExit(f"--strong: {a.nsub} subdomains do not split evenly over {world} GPUs")
+        return (a.ncell,) * 3, a.nsub
+    return tuple(a.ncell * k for k in gpu_grid(world)), a.nsub * world
+
+
 def workload_name(a, world):
     if a.workload == "q1cube":
         p = round(a.nsub ** (1 / 3))
         return (f"3D Q1 Poisson (27-point), channels coefficient 1e6, structured {a.ncell}^3 cells, {p}x{p}x{p} brick subdomains, "
                 f"overlap {a.overlap}, {a.coarse} coarse space nev {a.nev}, additive, CG 1e-8")
-    g = gpu_grid(world)
-    shape = tuple(a.ncell * k for k in g)
+    shape, nsub = job_shape(a, world)
     return (f"3D P1 Poisson on the unit cube, islands coefficient (poisson_coefficient.lua), Kuhn mesh {shape[0]}x{shape[1]}x{shape[2]} cells, "
-            f"{a.nsub * world} subdomains (RCB), overlap {a.overlap}, {a.coarse} coarse space nev {a.nev}, additive, CG 1e-8")
+            f"{nsub} subdomains (RCB), overlap {a.overlap}, {a.coarse} coarse space nev {a.nev}, additive, CG 1e-8")
 
 
 def build_problem(a, world, rank=None, gather=None):
@@ -81,7 +92,7 @@ def build_problem(a, world, rank=None, gather=None):
     if gather is not None:
         from ddm_b200.partition import sub_ranges
 
-        s0, s1 = sub_ranges(a.nsub * world, world)[rank]
+        s0, s1 = sub_ranges(job_shape(a, world)[1], world)[rank]
         kw.update(only=range(s0, s1), gather=gather, workers=max(1, (os.cpu_count() or 1) // world), assemble_part=(rank, world))
     P = _build_problem(a, world, fem, mesh, problem, **kw)
     if a.pack and gather is None:
@@ -99,10 +110,9 @@ def _build_problem(a, world, fem, mesh, problem, **kw):
     # reference scales (grid.refine + one rank per subdomain).  A first version tiled the coefficient pattern over a growing
     # box instead: with 8x8x8 subdomains the fixed nev = 16 GenEO space no longer captured all high-contrast inclusions and
     # PCG (GPU and CPU oracle alike) stagnated near 1e-6.
-    g = gpu_grid(world)
-    shape = tuple(a.ncell * k for k in g)
+    shape, nsub = job_shape(a, world)
     coords, cells = mesh.structured_simplices(shape, lengths=(1.0, 1.0, 1.0))
-    return problem.poisson_simplex(coords, cells, a.nsub * world, kappa_fn=fem.kappa_islands, xmax=1.0, overlap=a.overlap,
+    return problem.poisson_simplex(coords, cells, nsub, kappa_fn=fem.kappa_islands, xmax=1.0, overlap=a.overlap,
                                    coarse=a.coarse, nev=a.nev, meta=dict(mesh=f"kuhn-{shape}"), **kw)
 
 
@@ -198,7 +208,7 @@ def run_reference(a):
     t = float(np.mean(ts))
     val = P.n / t / 1e6
     line = {"impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": a.gpus, "steps": a.steps, "warmup": a.warmup,
-            "ms_per_step": t * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "ms_per_step": t * 1e3, "higher_is_better": True, "scaling": "strong" if a.strong else "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": {"workload": workload_name(a, max(world, a.gpus)), "dofs": int(P.n), "iterations": int(its_full), "converged": bool(conv)},
             "cpu_baseline": {"value": val, "unit": UNIT, "cores": nthreads, "kind": "port",
                              "sample": f"each step = first {m} of {its_full} PCG iterations, extrapolated by apply count; full solve measured once: {t_full_once:.1f} s"},
@@ -345,9 +355,11 @@ def run_b200(a):
         traffic = tr.get(f"{'' if a.workload == 'p1cube' else a.workload + '_'}ncell{a.ncell}_nsub{a.nsub}_{a.coarse}_nev{a.nev}_overlap{a.overlap}", {}).get(f"{dom}_kernel")
     except OSError:
         pass
+    if a.strong and world > 1:
+        traffic = None  # the capture is of one GPU holding all nsub subdomains
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": a.warmup, "ms_per_step": ms_step,
-        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "higher_is_better": True, "scaling": "strong" if a.strong else "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "config": {"workload": workload_name(a, world), "dofs": int(n), "subdomains": int(P.nsub), "coarse_dim": int(P.A0.shape[0]),
                    "factor_nnz": stats["factor_nnz"], "iterations": int(res.iterations), "converged": bool(res.converged),
                    "l2_policy": "inputs larger than L2 (factors %.1f GB per sweep vs 126 MB L2)" % (stats["trisolve_stored"] / 1e9)},

@@ -64,7 +64,7 @@ sys.path.insert(0, {root!r}); sys.path.insert(0, os.path.join({root!r}, "dune-dd
 import torch.distributed as dist, numpy as np
 import bench
 from ddm_b200 import partition
-sys.argv = ["bench.py", "--ncell", "8", "--nsub", "8", "--gpus", os.environ["WORLD_SIZE"]]
+sys.argv = ["bench.py", "--ncell", "8", "--nsub", "8", "--gpus", os.environ["WORLD_SIZE"]] + {extra!r}
 a = bench.parse()
 rank, world, local = bench.dist_env()
 dist.init_process_group("gloo")
@@ -76,7 +76,8 @@ P = bench.build_problem(a, world, rank, gather)
 S = partition.shard(P, rank, world)
 have = [i for i, F in enumerate(P.factors) if F is not None]
 assert have == list(range(*S.sub_range)), (have, S.sub_range)
-assert P.nsub == 8 * world and P.A0.shape[0] == sum(z.shape[1] for z in P.Z)
+assert P.nsub == (8 if a.strong else 8 * world) and (P.n == 9 ** 3 or not a.strong)
+assert P.A0.shape[0] == sum(z.shape[1] for z in P.Z) and bench.workload_name(a, world).count(f"{{P.nsub}} subdomains") == 1
 assert abs(P.A0 - P.A0.T).max() <= 1e-12 * abs(P.A0).max()
 sums = [None] * world
 dist.all_gather_object(sums, (float(abs(P.A0).sum()), float(abs(P.A).sum()), S.n_own))
@@ -86,15 +87,17 @@ dist.barrier()
 
 
 @pytest.mark.timeout(300)
-def test_bench_sharded_setup_under_torchrun(tmp_path):
-    """bench.py's N > 1 setup wiring (refined unit cube, 64 -> here 8 subdomains per rank, gloo exchange), 4 ranks on the CPU."""
+@pytest.mark.parametrize("extra", [[], ["--strong"]], ids=["weak", "strong"])
+def test_bench_sharded_setup_under_torchrun(tmp_path, extra):
+    """bench.py's N > 1 setup wiring (weak: refined unit cube, 64 -> here 8 subdomains per rank; strong: the N = 1 problem dealt
+    out), gloo exchange, 4 ranks on the CPU."""
     import socket
 
     with socket.socket() as s:
         s.bind(("127.0.0.1", 0))
         port = s.getsockname()[1]
     script = tmp_path / "bench_worker.py"
-    script.write_text(BENCH_WORKER.format(root=os.path.dirname(HERE)))
+    script.write_text(BENCH_WORKER.format(root=os.path.dirname(HERE), extra=extra))
     r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=4", "--master-addr", "127.0.0.1",
                         "--master-port", str(port), str(script)], capture_output=True, text=True, timeout=280)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-3000:]
