@@ -153,3 +153,28 @@ def test_q1_brick_family_converges():
     O = oracle.Oracle(P, nthreads=2)
     x, it, conv, hist = O.pcg(P.b, reduction=1e-8, maxit=100)
     assert conv and it < 60 and np.linalg.norm(P.b - P.A @ x) <= 1e-7 * np.linalg.norm(P.b)
+
+
+@pytest.mark.parametrize("kind", ["standard", "distance", "trivial"])
+def test_partition_of_unity_types(kind):
+    """The three PartitionOfUnityType values (pou.hh:24-32,79-141): each sums to one over the sharing subdomains; standard and
+    distance vanish on the subdomain boundary, trivial is the owner indicator; restricted Schwarz with any of them converges."""
+    from ddm_b200.setup import problem
+    from oracle import oracle
+
+    P = problem.unitcube_p1(8, 4, overlap=2, nev=4, workers=1, pou_kind=kind)
+    tot = np.zeros(P.n)
+    for s, w in zip(P.subs, P.pou):
+        np.add.at(tot, s, w)
+    assert np.max(np.abs(tot - 1.0)) <= 1e-12
+    for r, (s, w) in enumerate(zip(P.subs, P.pou)):
+        assert np.all(w >= 0.0) and np.all(w <= 1.0 + 1e-15)
+        if kind == "trivial":
+            assert np.array_equal(w, (P.owner[s] == r).astype(np.float64))
+        else:
+            assert (w == 0.0).any() and w[: int(P.n_novlp[r])].max() > 0.0  # zero on the subdomain boundary, not inside
+        if kind == "standard":  # 1 / (number of subdomains holding the DOF as a non-boundary DOF)
+            inv = 1.0 / w[w > 0]
+            assert np.allclose(inv, np.round(inv), atol=1e-12)
+    x, it, conv, _ = oracle.Oracle(P, nthreads=2).gmres(P.b, reduction=1e-8, restart=30, maxit=200, restricted=True)
+    assert conv and np.linalg.norm(P.b - P.A @ x) <= 1e-6 * np.linalg.norm(P.b)
