@@ -48,12 +48,28 @@ def neumann_matrices(n, cells, Ke, sub, shared_count, dirichlet):
     return A_neu, B_neu
 
 
-def geneo_basis(A_neu, B_neu, pou, dirichlet_local, nev=16, shift=1e-3, tol=1e-5, seed=1):
-    """Columns: pou-scaled, normalised eigenvectors for the nev smallest eigenvalues."""
+def threshold_count(ev, nev, nev_max, threshold):
+    """How many of the ascending eigenvalues `ev` the reference's retry loop ends up keeping (spectra.hh:118-163): it solves
+    for nev pairs, doubles nev while the largest one is still below the threshold and nev < nev_max, then keeps the pairs
+    below the threshold among the first nconv - 1 (at least one).  Returns (pairs computed in the last round, pairs kept)."""
+    n = int(nev)
+    while True:
+        nconv = min(n, len(ev))
+        if nconv == len(ev) or ev[nconv - 1] >= threshold or n >= nev_max:
+            break
+        n *= 2
+    cnt = 0
+    while cnt < nconv - 1 and ev[cnt] < threshold:
+        cnt += 1
+    return nconv, max(cnt, 1)
+
+
+def geneo_basis(A_neu, B_neu, pou, dirichlet_local, nev=16, shift=1e-3, tol=1e-5, seed=1, threshold=-0.5, nev_max=None):
+    """Columns: pou-scaled, normalised eigenvectors for the nev smallest eigenvalues -- or, with a positive threshold, for the
+    eigenvalues below it (nev doubled until the spectrum is covered or nev_max = 2 nev is reached, eigensolver_params.hh:20-30)."""
     n = A_neu.shape[0]
     D = sp.diags(pou)
     C = (D @ B_neu @ D).tocsc()
-    nev = min(nev, n - 2)
     rng = np.random.default_rng(seed)
     v0 = rng.standard_normal(n)
     # Shift to the left of the spectrum (all eigenvalues are >= 0): A + shift*C is SPD-like
@@ -64,19 +80,30 @@ def geneo_basis(A_neu, B_neu, pou, dirichlet_local, nev=16, shift=1e-3, tol=1e-5
     K = (A_neu + shift * C).tocsc()
     lu = spla.splu(K, permc_spec="MMD_AT_PLUS_A", diag_pivot_thresh=0.0, options=dict(SymmetricMode=True))
     OPinv = spla.LinearOperator((n, n), matvec=lu.solve, dtype=np.float64)
-    ncv = min(max(2 * nev, nev + 2), n - 1)
-    try:
-        w, V = spla.eigsh(A_neu.tocsc(), k=nev, M=C, sigma=-shift, which="LM", OPinv=OPinv, tol=tol, ncv=ncv, v0=v0, maxiter=1000)
-    except spla.ArpackNoConvergence as e:  # keep what converged, as the reference's retry loop would
-        w, V = e.eigenvalues, e.eigenvectors
-    order = np.argsort(w)
-    V = V[:, order]
+    Ac = A_neu.tocsc()
+    nev_max = 2 * nev if nev_max is None else nev_max
+    want = nev
+    while True:
+        k = min(want, n - 2)
+        ncv = min(max(2 * k, k + 2), n - 1)
+        try:
+            w, V = spla.eigsh(Ac, k=k, M=C, sigma=-shift, which="LM", OPinv=OPinv, tol=tol, ncv=ncv, v0=v0, maxiter=1000)
+        except spla.ArpackNoConvergence as e:  # keep what converged, as the reference's retry loop would
+            w, V = e.eigenvalues, e.eigenvectors
+        order = np.argsort(w)
+        w, V = w[order], V[:, order]
+        if threshold <= 0 or w.size == 0 or w[-1] >= threshold or want >= nev_max or k < want:
+            break
+        want *= 2  # spectra.hh:194-197: not enough eigenvalues below the threshold yet
+    if threshold > 0 and w.size:
+        keep_n = threshold_count(w, w.size, w.size, threshold)[1]
+        w, V = w[:keep_n], V[:, :keep_n]
     V = V * pou[:, None]
     V[dirichlet_local, :] = 0.0
     nrm = np.linalg.norm(V, axis=0)
     keep = nrm > 1e-14
     V = V[:, keep] / nrm[keep]
-    return np.asfortranarray(V), w[order][keep]
+    return np.asfortranarray(V), w[keep]
 
 
 def pou_template_basis(coords_local, pou, dirichlet_local, degree=1):

@@ -107,7 +107,8 @@ def _sub_job(i):
                     return i, F, np.zeros((s.size, 0), order="F")
                 FK = factor.cholesky_supernodal((An + g["shift"] * Cm).tocsr(), co, g["leaf_size"])
                 return i, F, (Cm, FK)
-            Zi, ev = coarse_mod.geneo_basis(An, Bn, g["pou"][i], dl, nev=g["nev"], shift=g["shift"], tol=g["eig_tol"])
+            Zi, ev = coarse_mod.geneo_basis(An, Bn, g["pou"][i], dl, nev=g["nev"], shift=g["shift"], tol=g["eig_tol"],
+                                            threshold=g["eig_threshold"], nev_max=g["nev_max"])
         elif kind == "pou":
             Zi = coarse_mod.pou_template_basis(g["coords"][s], g["pou"][i], dl)
         elif kind == "none":
@@ -119,7 +120,7 @@ def _sub_job(i):
 
 def build(coords, cells, Ke, dirichlet, rhs, cell_part, nsub, overlap=2, pou_kind="distance", shrink=0,
           coarse="geneo", nev=16, shift=1e-3, eig_tol=1e-5, leaf_size=32, workers=None, meta=None, only=None, gather=None,
-          A_full=None, symmetric=True, ke_fn=None, eigensolver="host", eig_device=0):
+          A_full=None, symmetric=True, ke_fn=None, eigensolver="host", eig_device=0, eig_threshold=-0.5, nev_max=None):
     """Generic pipeline from an element-wise description to SetupProducts.
 
     only / gather: with several processes (one per GPU) every process factors and builds the coarse basis of its own
@@ -175,7 +176,7 @@ def build(coords, cells, Ke, dirichlet, rhs, cell_part, nsub, overlap=2, pou_kin
     _G.clear()
     _G.update(A=A, subs=subs, coords=coords, cells=cells, Ke=Ke, dirichlet=dirichlet, shared=shared, pou=pou,
               coarse=coarse, nev=nev, shift=shift, eig_tol=eig_tol, leaf_size=leaf_size, symmetric=symmetric,
-              eigensolver=eigensolver if coarse == "geneo" else "host")
+              eigensolver=eigensolver if coarse == "geneo" else "host", eig_threshold=eig_threshold, nev_max=nev_max)
     workers = workers or min(max(len(todo), 1), os.cpu_count() or 1)
     factors = [None] * nsub
     Z = [None] * nsub
@@ -193,9 +194,16 @@ def build(coords, cells, Ke, dirichlet, rhs, cell_part, nsub, overlap=2, pou_kin
 
         batch = [i for i in todo if isinstance(Z[i], tuple)]
         if batch:
-            Zs, _ = geneo_gpu.batched_geneo([Z[i][0] for i in batch], [Z[i][1] for i in batch], [pou[i] for i in batch],
-                                            [dirichlet[subs[i]] for i in batch], nev=nev, shift=shift, tol=eig_tol, device=eig_device)
-            for i, Zi in zip(batch, Zs):
+            # eigenvalue threshold (eigensolver_params.hh:30,51): the lock-step solve computes the largest count the reference's
+            # doubling could reach, the per-subdomain selection then follows its retry loop (spectra.hh:118-163)
+            cap, top = nev, (2 * nev if nev_max is None else nev_max)
+            while eig_threshold > 0 and cap < top:
+                cap *= 2
+            Zs, evs = geneo_gpu.batched_geneo([Z[i][0] for i in batch], [Z[i][1] for i in batch], [pou[i] for i in batch],
+                                              [dirichlet[subs[i]] for i in batch], nev=cap, shift=shift, tol=eig_tol, device=eig_device)
+            for i, Zi, ev in zip(batch, Zs, evs):
+                if eig_threshold > 0 and ev.size:
+                    Zi = np.asfortranarray(Zi[:, : coarse_mod.threshold_count(ev, nev, top, eig_threshold)[1]])
                 Z[i] = Zi
     tick("factor + coarse basis")
     if gather is None:

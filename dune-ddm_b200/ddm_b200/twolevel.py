@@ -161,7 +161,7 @@ class TwoLevelSchwarzPreconditioner:
     problem: dict with the keys of setup.problem.build -- coords, cells, Ke (element matrices, or ke_fn), dirichlet, rhs,
     cell_part, nsub; optional A_full, symmetric.  ptree keys (defaults as in the reference): overlap (1, pdelab_schwarz.hh:44),
     coarsespace.type (geneo; supported here: geneo, pou, none -- the other types of :56-63 raise like Dune::NotImplemented),
-    coarse_space.nev / shift / tolerance (eigensolver_params.hh:43-51), pou.type / pou.shrink, schwarz.type (restricted,
+    coarse_space.nev / shift / tolerance / threshold / nev_max (eigensolver_params.hh:20-51), pou.type / pou.shrink, schwarz.type (restricted,
     schwarz.hh:80), combined_preconditioner.mode (additive, combined_preconditioner.hh:57).
     """
 
@@ -174,6 +174,7 @@ class TwoLevelSchwarzPreconditioner:
         from .setup import problem as setup_problem
 
         cfg = {"overlap": 1, "coarsespace.type": "geneo", "coarse_space.nev": 16, "coarse_space.shift": 1e-3, "coarse_space.tolerance": 1e-5,
+               "coarse_space.threshold": -0.5, "coarse_space.nev_max": None,
                "pou.type": "distance", "pou.shrink": 0, "schwarz.type": "restricted", "combined_preconditioner.mode": "additive"}
         cfg.update(ptree or {})
         kind = cfg["coarsespace.type"]
@@ -186,6 +187,7 @@ class TwoLevelSchwarzPreconditioner:
         self.P = setup_problem.build(p["coords"], p["cells"], p.get("Ke"), p["dirichlet"], p["rhs"], p["cell_part"], p["nsub"],
                                      overlap=cfg["overlap"], pou_kind=cfg["pou.type"], shrink=cfg["pou.shrink"], coarse=kind,
                                      nev=cfg["coarse_space.nev"], shift=cfg["coarse_space.shift"], eig_tol=cfg["coarse_space.tolerance"],
+                                     eig_threshold=cfg["coarse_space.threshold"], nev_max=cfg["coarse_space.nev_max"],
                                      workers=workers, A_full=p.get("A_full"), symmetric=p.get("symmetric", True), ke_fn=p.get("ke_fn"))
         has_coarse = self.P.A0.shape[0] > 0
         self.ctx = api.Context.from_products(self.P, device=device, with_coarse=has_coarse)

@@ -63,3 +63,38 @@ def test_step_limit_is_reported(monkeypatch):
     with pytest.warns(RuntimeWarning, match="did not reach tolerance"):
         Z, lams = geneo_gpu.batched_geneo(Cs, Ks, P.pou, [P.dirichlet[s] for s in P.subs], nev=5, shift=1e-3, tol=1e-12, m0=8, mmax=8)
     assert all(z.shape[1] <= 5 for z in Z)
+
+
+def test_threshold_count_follows_the_reference_retry_loop():
+    """spectra.hh:118-163 on plain numbers: nev doubles while the largest computed eigenvalue is below the threshold and
+    nev < nev_max; the kept pairs are those below the threshold among the first nconv - 1, at least one."""
+    from ddm_b200.setup.coarse import threshold_count
+
+    ev = np.array([0.0, 0.1, 0.2, 0.3, 0.6, 0.7, 0.8, 0.9])
+    assert threshold_count(ev, 4, 8, 0.25) == (4, 3)  # ev[3] >= thr: stop at nev, keep 0.0 0.1 0.2
+    assert threshold_count(ev, 4, 8, 0.65) == (8, 5)  # ev[3] < thr: double, then five below
+    assert threshold_count(ev, 4, 8, 5.0) == (8, 7)  # everything below: nev_max reached, the loop stops one short of nconv
+    assert threshold_count(ev + 1.0, 4, 8, 0.5) == (4, 1)  # nothing below: one vector is kept anyway
+    assert threshold_count(ev, 2, 8, 0.65) == (8, 5)  # 2 -> 4 -> 8
+
+
+def test_eigenvalue_threshold_gives_ragged_coarse_spaces(monkeypatch):
+    """threshold > 0 (eigensolver_params.hh:30): every subdomain keeps the eigenvectors below it -- different counts per
+    subdomain --, host ARPACK path and batched path (host stand-in) select the same numbers, the method converges."""
+    from ddm_b200 import api
+    from ddm_b200.setup import problem
+    from oracle import oracle
+
+    import lanczos_standin
+
+    kw = dict(overlap=2, nev=4, workers=1, eig_threshold=0.95, nev_max=8)
+    Ph = problem.unitcube_p1(10, 6, **kw)
+    ks = [z.shape[1] for z in Ph.Z]
+    assert min(ks) >= 1 and max(ks) <= 7 and len(set(ks)) > 1, ks
+    assert Ph.A0.shape[0] == sum(ks)
+    monkeypatch.setattr(api.Context, "from_products", lanczos_standin.HostContext.from_products)
+    Pg = problem.unitcube_p1(10, 6, eigensolver="gpu", **kw)
+    assert [z.shape[1] for z in Pg.Z] == ks
+    x, it, conv, _ = oracle.Oracle(Ph, nthreads=2).pcg(Ph.b, reduction=1e-8, maxit=200)
+    y, it2, conv2, _ = oracle.Oracle(Pg, nthreads=2).pcg(Pg.b, reduction=1e-8, maxit=200)
+    assert conv and conv2 and abs(it - it2) <= 1 and np.linalg.norm(x - y) <= 1e-6 * np.linalg.norm(x)

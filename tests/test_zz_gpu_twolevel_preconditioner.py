@@ -57,3 +57,31 @@ def test_preconditioner_object_matches_the_oracle(kind):
         assert np.linalg.norm(x.download() - xo) <= 1e-8 * np.linalg.norm(xo)
     finally:
         T.close()
+
+
+@pytest.mark.gpu
+def test_ragged_coarse_space_from_an_eigenvalue_threshold():
+    """coarse_space.threshold > 0 (eigensolver_params.hh:30, spectra.hh:157-163): subdomains keep different numbers of
+    eigenvectors; the device path (ragged k_i in ddm_upload_coarse) applies like the oracle."""
+    from ddm_b200 import api, twolevel
+    from oracle import oracle
+
+    T = twolevel.TwoLevelSchwarzPreconditioner(_problem(10, 6), {"overlap": 2, "coarse_space.nev": 4, "coarse_space.nev_max": 8, "coarse_space.threshold": 0.95,
+                                                                "schwarz.type": "standard"}, workers=1)
+    try:
+        P, ctx = T.P, T.ctx
+        ks = [z.shape[1] for z in P.Z]
+        assert len(set(ks)) > 1 and P.A0.shape[0] == sum(ks)
+        O = oracle.Oracle(P, nthreads=2)
+        d = np.random.default_rng(2).standard_normal(P.n)
+        v = ctx.vector()
+        T.apply(v, ctx.vector(d))
+        want = O.twolevel_apply(d)
+        tol = max(1e-12, 8 * np.finfo(float).eps * max([np.linalg.cond(P.A0)] + [np.linalg.cond(P.A[s][:, s].toarray()) for s in P.subs]))
+        assert np.linalg.norm(v.download() - want) <= tol * np.linalg.norm(want)
+        xo, ito, convo, _ = O.pcg(P.b, reduction=1e-8, maxit=200)
+        x, b = ctx.vector(np.zeros(P.n)), ctx.vector(P.b)
+        res = api.CGSolver(T.getNonOverlappingOperator(), T.getScalarProduct(), T.combined, reduction=1e-8, maxit=200).solve_device(x, b)
+        assert res.converged and convo and abs(res.iterations - ito) <= 1
+    finally:
+        T.close()
