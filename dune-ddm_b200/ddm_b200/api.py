@@ -88,9 +88,10 @@ class Context:
         self.world = 1
 
     @classmethod
-    def from_products(cls, P, device=0, rank=0, world=1, unique_id=None, with_coarse=True, device_galerkin=False):
+    def from_products(cls, P, device=0, rank=0, world=1, unique_id=None, with_coarse=True, device_galerkin=False, with_pou=True):
         """Upload the setup products (whole problem, or this rank's shard).  device_galerkin: do not upload P.A0 but
-        assemble Z^T A Z on the GPU (ddm_galerkin_assemble); the result is kept in self.A0_device."""
+        assemble Z^T A Z on the GPU (ddm_galerkin_assemble); the result is kept in self.A0_device.  with_pou=False uploads no
+        partition of unity: restricted Schwarz then applies no weights (schwarz.hh:140, pou == nullptr)."""
         self = cls(device)
         S = shard(P, rank, world)
         self.shard, self.world, self.rank = S, world, rank
@@ -118,7 +119,7 @@ class Context:
         a, b = S.sub_range
         pou = np.concatenate([P.pou[i] for i in range(a, b)]).astype(np.float64) if b > a else np.zeros(0)
         check(lib.ddm_upload_decomposition(self.h, C.c_int32(b - a), _p(S.sub_ptr, C.c_int64), _p(S.sub_dofs, C.c_int32),
-                                           _p(pou, C.c_double)))
+                                           _p(pou, C.c_double) if with_pou else None))
         self.upload_factors(P, a, b)
         N0 = int(P.A0.shape[0])
         self.N0 = N0 if with_coarse else 0

@@ -94,3 +94,22 @@ def test_wrong_vector_length_is_refused(env):
     P, ctx, *_ = env
     with pytest.raises(DDMError):
         ctx.vector(np.zeros(P.n + 1))
+
+
+def test_restricted_schwarz_without_a_partition_of_unity(small3d):
+    """schwarz.hh:138-141: the weights are applied only when a partition of unity was given; without one the restricted variant
+    is the plain sum over the subdomains, i.e. what the standard variant computes."""
+    from ddm_b200 import api
+    from oracle import oracle
+
+    P = small3d
+    ctx = api.Context.from_products(P, with_pou=False)
+    try:
+        d = np.random.default_rng(9).standard_normal(P.n)
+        x = ctx.vector()
+        api.SchwarzPreconditioner(ctx, "restricted").apply(x, ctx.vector(d))
+        want = oracle.Oracle(P, nthreads=2).schwarz_apply(d, restricted=False)
+        tol = max(1e-12, 8 * np.finfo(float).eps * max(np.linalg.cond(P.A[s][:, s].toarray()) for s in P.subs))
+        assert np.linalg.norm(x.download() - want) <= tol * np.linalg.norm(want)
+    finally:
+        ctx.close()
