@@ -306,6 +306,15 @@ def unitcube_p1(ncell, nsub, **kw):
     return poisson_simplex(coords, cells, nsub, meta=dict(mesh=f"kuhn-{ncell}^3"), **kw)
 
 
+def poisson_gmsh(path, dim, nsub, refine=0, **kw):
+    """Configs C1 / C2 on the reference's own meshes: Gmsh 2.2 file (data/unitsquare.msh, data/unitcube.msh), `refine` uniform
+    refinements (grid->globalRefine, examples/poisson.cc:87-139), islands coefficient, Dirichlet data on x in {0, 1}."""
+    coords, cells = mesh.read_gmsh22(path, dim)
+    for _ in range(int(refine)):
+        coords, cells = mesh.refine_simplices(coords, cells)
+    return poisson_simplex(coords, cells, nsub, meta=dict(mesh=f"{os.path.basename(path)} refined {int(refine)}x"), **kw)
+
+
 def unitsquare_p1(ncell, nsub, **kw):
     coords, cells = mesh.structured_simplices((ncell,) * 2)
     return poisson_simplex(coords, cells, nsub, meta=dict(mesh=f"kuhn-{ncell}^2"), **kw)
