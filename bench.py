@@ -41,7 +41,7 @@ def parse():
     ap.add_argument("--nsub", type=int, default=64, help="subdomains per GPU")
     ap.add_argument("--workload", default="p1cube", choices=["p1cube", "q1cube"],
                     help="p1cube: BASELINE.json configs[1] (default, the metric's configuration); q1cube: configs[4]'s family (structured Q1, "
-                         "27-point, channels coefficient, brick subdomains; --ncell cells per axis, nsub must be a cube; N=1 only)")
+                         "27-point, channels coefficient, brick subdomains; --ncell cells per axis and GPU, nsub must be a cube)")
     ap.add_argument("--coarse", default="geneo", choices=["geneo", "pou"])
     ap.add_argument("--nev", type=int, default=16)
     ap.add_argument("--eigensolver", default=os.environ.get("DDM_BENCH_EIGENSOLVER", "host"), choices=["host", "gpu"],
@@ -70,11 +70,25 @@ def job_shape(a, world):
     return tuple(a.ncell * k for k in gpu_grid(world)), a.nsub * world
 
 
+def brick_grids(a, world):
+    """q1cube: (brick grid of the whole job, GPU grid that groups the bricks).  nsub = p^3 bricks per GPU (weak) or in total (strong)."""
+    p = round(a.nsub ** (1 / 3))
+    g = gpu_grid(world)
+    if p ** 3 != a.nsub:
+        raise SystemExit("--workload q1cube needs a cubic --nsub")
+    if a.strong:
+        if any(p % k for k in g):
+            raise SystemExit(f"--strong: a {p}x{p}x{p} brick grid does not split over the {g} GPU grid")
+        return (p, p, p), g
+    return tuple(p * k for k in g), g
+
+
 def workload_name(a, world):
     if a.workload == "q1cube":
-        p = round(a.nsub ** (1 / 3))
-        return (f"3D Q1 Poisson (27-point), channels coefficient 1e6, structured {a.ncell}^3 cells, {p}x{p}x{p} brick subdomains, "
-                f"overlap {a.overlap}, {a.coarse} coarse space nev {a.nev}, additive, CG 1e-8")
+        shape, _ = job_shape(a, world)
+        pg, _ = brick_grids(a, world)
+        return (f"3D Q1 Poisson (27-point) on the unit cube, channels coefficient 1e6, structured {shape[0]}x{shape[1]}x{shape[2]} cells, "
+                f"{pg[0]}x{pg[1]}x{pg[2]} brick subdomains, overlap {a.overlap}, {a.coarse} coarse space nev {a.nev}, additive, CG 1e-8")
     shape, nsub = job_shape(a, world)
     return (f"3D P1 Poisson on the unit cube, islands coefficient (poisson_coefficient.lua), Kuhn mesh {shape[0]}x{shape[1]}x{shape[2]} cells, "
             f"{nsub} subdomains (RCB), overlap {a.overlap}, {a.coarse} coarse space nev {a.nev}, additive, CG 1e-8")
@@ -102,10 +116,11 @@ def build_problem(a, world, rank=None, gather=None):
 
 def _build_problem(a, world, fem, mesh, problem, **kw):
     if a.workload == "q1cube":
-        p = round(a.nsub ** (1 / 3))
-        if p ** 3 != a.nsub or world != 1:
-            raise SystemExit("--workload q1cube needs a cubic --nsub and one GPU")
-        return problem.poisson_q1_cube(a.ncell, (p, p, p), overlap=a.overlap, coarse=a.coarse, nev=a.nev, **kw)
+        # config C5's family: with N GPUs the unit cube is refined by the GPU grid and every GPU hosts a p x p x p block of bricks
+        # (8x8x8 subdomains -> 2x2x2 GPU bricks of 4x4x4); CPU oracle: 28 -> 29 iterations from 1 to 8 GPUs at 32 cells per GPU axis
+        shape, _ = job_shape(a, world)
+        pg, g = brick_grids(a, world)
+        return problem.poisson_q1_cube(shape if world > 1 else a.ncell, pg, group=g, overlap=a.overlap, coarse=a.coarse, nev=a.nev, **kw)
     # Weak scaling = the same problem (unit cube, same coefficient) on a finer mesh with more subdomains, 64 per GPU, as the
     # reference scales (grid.refine + one rank per subdomain).  A first version tiled the coefficient pattern over a growing
     # box instead: with 8x8x8 subdomains the fixed nev = 16 GenEO space no longer captured all high-contrast inclusions and

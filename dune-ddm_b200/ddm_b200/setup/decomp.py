@@ -51,13 +51,25 @@ def rcb_partition(points, nparts):
     return part
 
 
-def box_partition(shape, pgrid):
-    """Partition the cells of a structured grid into a pgrid[0] x pgrid[1] x ... brick layout."""
+def box_partition(shape, pgrid, group=None):
+    """Partition the cells of a structured grid into a pgrid[0] x pgrid[1] x ... brick layout.
+
+    group = (gx, gy, ...): bricks are numbered so that each of the gx * gy * ... equal blocks of the brick grid owns a
+    contiguous range of part ids (block-major, then brick-lexicographic inside the block) -- one block per GPU, the
+    partitioning of SURVEY 8(e): 8 x 8 x 8 subdomains -> 2 x 2 x 2 GPU bricks of 4 x 4 x 4."""
     idx = np.meshgrid(*[np.arange(s) for s in shape], indexing="ij")
-    part = np.zeros(shape, dtype=np.int32)
-    for ax, (s, p) in enumerate(zip(shape, pgrid)):
-        part = part * p + (idx[ax] * p) // s
-    return part.ravel()
+    bricks = [(idx[ax] * p) // s for ax, (s, p) in enumerate(zip(shape, pgrid))]
+    if group is None:
+        group = (1,) * len(shape)
+    per = [p // g for p, g in zip(pgrid, group)]
+    if any(p % g for p, g in zip(pgrid, group)):
+        raise ValueError(f"brick grid {tuple(pgrid)} does not split into {tuple(group)} equal blocks")
+    blk = np.zeros(shape, dtype=np.int32)
+    loc = np.zeros(shape, dtype=np.int32)
+    for ax in range(len(shape)):
+        blk = blk * group[ax] + bricks[ax] // per[ax]
+        loc = loc * per[ax] + bricks[ax] % per[ax]
+    return (blk * int(np.prod(per)) + loc).ravel().astype(np.int32)
 
 
 def nonoverlapping_sets(n, cells, cell_part, nparts):

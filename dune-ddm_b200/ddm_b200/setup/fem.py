@@ -106,9 +106,35 @@ def _q1_reference_matrix():
     return K
 
 
+def _q1_directional_matrices():
+    """8x8 matrices int d_a phi_i d_a phi_j on the unit cube for a = x, y, z (2-point Gauss), node order as structured_q1."""
+    gp = np.array([0.5 - 0.5 / np.sqrt(3.0), 0.5 + 0.5 / np.sqrt(3.0)])
+    K = np.zeros((3, 8, 8))
+    corners = [(a, b, c) for a in (0, 1) for b in (0, 1) for c in (0, 1)]
+    for qx in gp:
+        for qy in gp:
+            for qz in gp:
+                g = np.zeros((8, 3))
+                for n, (a, b, c) in enumerate(corners):
+                    fx, dfx = (qx, 1.0) if a else (1 - qx, -1.0)
+                    fy, dfy = (qy, 1.0) if b else (1 - qy, -1.0)
+                    fz, dfz = (qz, 1.0) if c else (1 - qz, -1.0)
+                    g[n] = (dfx * fy * fz, fx * dfy * fz, fx * fy * dfz)
+                for ax in range(3):
+                    K[ax] += np.outer(g[:, ax], g[:, ax]) / 8.0
+    return K
+
+
 def q1_element_matrices(h, kappa):
-    """Q1 stiffness on cubes of edge h: kappa * h * K_ref; (m, 8, 8)."""
-    return (kappa * h)[:, None, None] * _q1_reference_matrix()[None]
+    """Q1 stiffness on bricks; (m, 8, 8).  h scalar: cubes of edge h, kappa * h * K_ref.  h = (hx, hy, hz): bricks,
+    kappa * (hy hz / hx Kx + hx hz / hy Ky + hx hy / hz Kz) (the refined unit cube of the multi-GPU family is split unevenly
+    over the axes for 2 and 4 GPUs)."""
+    if np.ndim(h) == 0:
+        return (kappa * h)[:, None, None] * _q1_reference_matrix()[None]
+    hx, hy, hz = (float(v) for v in h)
+    Kd = _q1_directional_matrices()
+    Kb = (hy * hz / hx) * Kd[0] + (hx * hz / hy) * Kd[1] + (hx * hy / hz) * Kd[2]
+    return kappa[:, None, None] * Kb[None]
 
 
 def assemble(n, cells, Ke, subset=None):

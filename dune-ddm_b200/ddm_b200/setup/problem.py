@@ -224,6 +224,25 @@ def build(coords, cells, Ke, dirichlet, rhs, cell_part, nsub, overlap=2, pou_kin
 
 
 # ----------------------------------------------------------------------------- named configurations
+def _assemble_global(n, cells, ke_fn, kw, chunk=4_000_000):
+    """The assembled matrix before Dirichlet elimination.  kw["assemble_part"] = (rank, world) together with kw["gather"]: every
+    process assembles its slice of the cells, the partial matrices are exchanged and summed in rank order; otherwise one process
+    assembles chunk by chunk (element matrices never all at once), the chunks in parallel workers."""
+    part_of = kw.pop("assemble_part", None)
+    if part_of is not None and kw.get("gather") is not None:
+        r, w = part_of
+        lo, hi = cells.shape[0] * r // w, cells.shape[0] * (r + 1) // w
+        A_loc = fem.assemble_chunked(n, cells[lo:hi], lambda idx: ke_fn(idx + lo), chunk=chunk)
+        A_full = None
+        for ip, ix, da in kw["gather"]((A_loc.indptr, A_loc.indices, A_loc.data)):
+            Ap = sp.csr_matrix((da, ix, ip), shape=(n, n))
+            A_full = Ap if A_full is None else A_full + Ap
+        A_full.sum_duplicates()
+        A_full.sort_indices()
+        return A_full
+    return fem.assemble_chunked(n, cells, ke_fn, chunk=chunk, workers=kw.get("workers") or (os.cpu_count() or 1))
+
+
 def poisson_simplex(coords, cells, nsub, kappa_fn=fem.kappa_islands, xmax=1.0, **kw):
     """P1 Poisson with Dirichlet data g = 1 - x/xmax on x in {0, xmax} (poisson_coefficient.lua:1-3,38-44)."""
     import time
@@ -248,21 +267,7 @@ def poisson_simplex(coords, cells, nsub, kappa_fn=fem.kappa_islands, xmax=1.0, *
     dirichlet = (coords[:, 0] < 1e-6) | (coords[:, 0] > xmax - 1e-6)
     n = coords.shape[0]
     tick("coefficient")
-    part_of = kw.pop("assemble_part", None)
-    if part_of is not None and kw.get("gather") is not None:
-        # several processes: each assembles its slice of the cells, the partial matrices are exchanged and summed in rank order
-        r, w = part_of
-        lo, hi = cells.shape[0] * r // w, cells.shape[0] * (r + 1) // w
-        A_loc = fem.assemble_chunked(n, cells[lo:hi], lambda idx: ke_fn(idx + lo))
-        A_full = None
-        for ip, ix, da in kw["gather"]((A_loc.indptr, A_loc.indices, A_loc.data)):
-            Ap = sp.csr_matrix((da, ix, ip), shape=(n, n))
-            A_full = Ap if A_full is None else A_full + Ap
-        A_full.sum_duplicates()
-        A_full.sort_indices()
-    else:
-        # element matrices are produced chunk by chunk, never all at once; one process: chunks in parallel
-        A_full = fem.assemble_chunked(n, cells, ke_fn, workers=kw.get("workers") or (os.cpu_count() or 1))
+    A_full = _assemble_global(n, cells, ke_fn, kw)
     # residual at the Dirichlet lift x0 (g on the boundary, 0 inside): d = A_full x0 - f, f = 0
     x0 = np.where(dirichlet, 1.0 - coords[:, 0] / xmax, 0.0)
     rhs = A_full @ x0
@@ -273,10 +278,12 @@ def poisson_simplex(coords, cells, nsub, kappa_fn=fem.kappa_islands, xmax=1.0, *
     return build(coords, cells, None, dirichlet, rhs, part, nsub, meta=meta, A_full=A_full, ke_fn=ke_fn, **kw)
 
 
-def poisson_q1_cube(ncell, pgrid, kappa_fn=fem.kappa_channels, **kw):
-    """Structured Q1 Poisson on the unit cube, brick decomposition (config C5 family).  Element matrices are produced chunk by
-    chunk (64 doubles per cell: 6 GB at the 231^3 cells of one C5 GPU share if held at once)."""
-    shape = (ncell,) * 3
+def poisson_q1_cube(ncell, pgrid, kappa_fn=fem.kappa_channels, group=None, **kw):
+    """Structured Q1 Poisson on the unit cube, brick decomposition (config C5 family).  ncell: cells per axis, or one count per
+    axis (the multi-GPU family refines the cube by the GPU grid, so 2 and 4 GPUs work on bricks instead of cubes); group: GPU
+    grid for the brick numbering (decomp.box_partition).  Element matrices are produced chunk by chunk (64 doubles per cell:
+    6 GB at the 231^3 cells of one C5 GPU share if held at once)."""
+    shape = (int(ncell),) * 3 if np.ndim(ncell) == 0 else tuple(int(c) for c in ncell)
     coords, cells = mesh.structured_q1(shape)
     cent = coords[cells[:, 0]]
     for k in range(1, cells.shape[1]):
@@ -284,19 +291,19 @@ def poisson_q1_cube(ncell, pgrid, kappa_fn=fem.kappa_channels, **kw):
     cent = cent / cells.shape[1]
     kap = kappa_fn(cent)
     del cent
-    h = 1.0 / ncell
+    h = 1.0 / shape[0] if len(set(shape)) == 1 else tuple(1.0 / c for c in shape)
 
     def ke_fn(idx):
         return fem.q1_element_matrices(h, kap[idx])
 
     n = coords.shape[0]
     dirichlet = (coords[:, 0] < 1e-9) | (coords[:, 0] > 1.0 - 1e-9)
-    A_full = fem.assemble_chunked(n, cells, ke_fn, chunk=1_000_000, workers=kw.get("workers") or (os.cpu_count() or 1))
+    A_full = _assemble_global(n, cells, ke_fn, kw, chunk=1_000_000)
     x0 = np.where(dirichlet, 1.0 - coords[:, 0], 0.0)
     rhs = A_full @ x0
-    part = decomp.box_partition(shape, pgrid)
+    part = decomp.box_partition(shape, pgrid, group)
     nsub = int(np.prod(pgrid))
-    meta = dict(kw.pop("meta", {}), problem="poisson-q1", dim=3, ncell=ncell, pgrid=tuple(pgrid))
+    meta = dict(kw.pop("meta", {}), problem="poisson-q1", dim=3, ncell=shape, pgrid=tuple(pgrid))
     return build(coords, cells, None, dirichlet, rhs, part, nsub, meta=meta, A_full=A_full, ke_fn=ke_fn, **kw)
 
 
