@@ -44,3 +44,13 @@ def elast():
     from ddm_b200.setup import problem
 
     return problem.elasticity_box(3, 6, nev=8, workers=1)
+
+
+def pytest_collection_modifyitems(config, items):
+    """GPU tests get a hard time limit (pytest-timeout, thread method: the process is ended even when the main thread sits in a
+    CUDA synchronize), so that a kernel that never finishes costs one test run and not the GPU box."""
+    if not config.pluginmanager.hasplugin("timeout"):
+        return
+    for item in items:
+        if item.get_closest_marker("gpu") and not item.get_closest_marker("timeout"):
+            item.add_marker(pytest.mark.timeout(900, method="thread"))
