@@ -15,3 +15,10 @@ timeout 900 ncu --set full --clock-control none --import-source on -k 'regex:tri
     python bench.py --pack $PACK --steps 1 --warmup 3 --no-cpu-baseline > $OUT/${TAG}_ncu_full.log 2>&1; echo "set full exit $?"
 DDM_SETUP_VERBOSE=1 timeout 900 python bench.py --eigensolver gpu --steps 2 --warmup 3 --no-cpu-baseline > $OUT/${TAG}_bench_eiggpu.json 2> $OUT/${TAG}_bench_eiggpu.err
 echo "device eigensolve exit $?"; grep -i "geneo\|eigen\|setup" $OUT/${TAG}_bench_eiggpu.err | tail -5; tail -1 $OUT/${TAG}_bench_eiggpu.json | cut -c1-600
+# (7) optional, C5=1: config C5's per-GPU unit (232^3 nodes, 64 bricks of <= 62^3 overlapped nodes, about 100 GB of tiles), POU coarse space
+if [ -n "$C5" ]; then
+    free -g | head -2
+    DDM_SETUP_VERBOSE=1 timeout 2400 python bench.py --workload q1cube --ncell 231 --nsub 64 --coarse pou --steps 2 --warmup 3 --no-cpu-baseline \
+        > $OUT/${TAG}_bench_c5unit.json 2> $OUT/${TAG}_bench_c5unit.err
+    echo "C5 unit exit $?"; tail -3 $OUT/${TAG}_bench_c5unit.err; tail -1 $OUT/${TAG}_bench_c5unit.json | cut -c1-900
+fi
