@@ -1523,14 +1523,28 @@ extern "C" int ddm_blockdiag_solve(ddm_ctx *c, ddm_vec *d, ddm_vec *x)
 }
 
 // ------------------------------------------------------------------------------------------------ PCG
+struct EventPair {
+    cudaEvent_t a = nullptr, b = nullptr;
+    int create()
+    {
+        CU(cudaEventCreate(&a));
+        CU(cudaEventCreate(&b));
+        return 0;
+    }
+    ~EventPair()
+    {
+        if (a) cudaEventDestroy(a);
+        if (b) cudaEventDestroy(b);
+    }
+};
 extern "C" int ddm_pcg_solve(ddm_ctx *c, ddm_vec *b, ddm_vec *x, double reduction, int32_t maxit, int type, int mode,
                              int with_coarse, ddm_result *res, double *history)
 {
     CK(need_final(c));
     ddm_vec *p = c->tmp[0], *q = c->tmp[1];
-    cudaEvent_t e0, e1;
-    CU(cudaEventCreate(&e0));
-    CU(cudaEventCreate(&e1));
+    EventPair ev;  // destroyed on every return path (a NaN defect or a breakdown leaves through fail())
+    CK(ev.create());
+    cudaEvent_t &e0 = ev.a, &e1 = ev.b;
     CU(cudaEventRecord(e0, c->s));
     // scal slots: 0 scratch, 1 alpha, 2 def^2, 3/4 rho (alternating)
     CK(spmv(c, x->d, b->d, -1.0, 1)); // b <- b - A x
@@ -1573,8 +1587,6 @@ extern "C" int ddm_pcg_solve(ddm_ctx *c, ddm_vec *b, ddm_vec *x, double reductio
     CU(cudaEventSynchronize(e1));
     float ms = 0;
     CU(cudaEventElapsedTime(&ms, e0, e1));
-    cudaEventDestroy(e0);
-    cudaEventDestroy(e1);
     if (res) {
         res->iterations = i;
         res->converged = conv ? 1 : 0;
@@ -1628,9 +1640,9 @@ extern "C" int ddm_gmres_solve(ddm_ctx *c, ddm_vec *b, ddm_vec *x, double reduct
     }
     ddm_vec **v = c->gm_v.data(), *w = c->gm_v[m + 1], *b2 = c->gm_v[m + 2];
     std::vector<double> s(m + 1), sn(m), cs(m), H((size_t)(m + 1) * m, 0.0);
-    cudaEvent_t e0, e1;
-    CU(cudaEventCreate(&e0));
-    CU(cudaEventCreate(&e1));
+    EventPair ev;  // destroyed on every return path (a NaN defect or a breakdown leaves through fail())
+    CK(ev.create());
+    cudaEvent_t &e0 = ev.a, &e1 = ev.b;
     CU(cudaEventRecord(e0, c->s));
     auto dot_to = [&](const double *vk, const double *vprev, const double *hprev, int slot) -> int {
         LAUNCH(c, mgs_kernel, c->nred, 256, n, hprev, vprev, vk, w->d, c->partial);
@@ -1705,8 +1717,6 @@ extern "C" int ddm_gmres_solve(ddm_ctx *c, ddm_vec *b, ddm_vec *x, double reduct
     CU(cudaEventSynchronize(e1));
     float ms = 0;
     CU(cudaEventElapsedTime(&ms, e0, e1));
-    cudaEventDestroy(e0);
-    cudaEventDestroy(e1);
     if (res) {
         res->iterations = j - 1;
         res->converged = conv ? 1 : 0;
