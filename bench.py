@@ -47,6 +47,9 @@ def parse():
     ap.add_argument("--eigensolver", default=os.environ.get("DDM_BENCH_EIGENSOLVER", "host"), choices=["host", "gpu"],
                     help="GenEO eigenproblems (setup, untimed): per-subdomain ARPACK on the host, or the batched device Lanczos")
     ap.add_argument("--overlap", type=int, default=2)
+    ap.add_argument("--eig-threshold", type=float, default=-0.5,
+                    help="GenEO: keep the eigenvectors below this eigenvalue instead of a fixed count (eigensolver_params.hh:30; <= 0: off, the default)")
+    ap.add_argument("--nev-max", type=int, default=None, help="GenEO with --eig-threshold: upper limit of the doubling of nev (default 2 nev)")
     ap.add_argument("--cpu-seconds", type=float, default=20.0, help="budget of the cpu_baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--pack", default=None, help=".ddmpack cache of the setup products: loaded if present, else built and saved")
@@ -90,8 +93,9 @@ def workload_name(a, world):
         return (f"3D Q1 Poisson (27-point) on the unit cube, channels coefficient 1e6, structured {shape[0]}x{shape[1]}x{shape[2]} cells, "
                 f"{pg[0]}x{pg[1]}x{pg[2]} brick subdomains, overlap {a.overlap}, {a.coarse} coarse space nev {a.nev}, additive, CG 1e-8")
     shape, nsub = job_shape(a, world)
+    thr = f" threshold {a.eig_threshold:g} (nev <= {a.nev_max or 2 * a.nev})" if a.eig_threshold > 0 and a.coarse == "geneo" else ""
     return (f"3D P1 Poisson on the unit cube, islands coefficient (poisson_coefficient.lua), Kuhn mesh {shape[0]}x{shape[1]}x{shape[2]} cells, "
-            f"{nsub} subdomains (RCB), overlap {a.overlap}, {a.coarse} coarse space nev {a.nev}, additive, CG 1e-8")
+            f"{nsub} subdomains (RCB), overlap {a.overlap}, {a.coarse} coarse space nev {a.nev}{thr}, additive, CG 1e-8")
 
 
 def build_problem(a, world, rank=None, gather=None):
@@ -101,6 +105,8 @@ def build_problem(a, world, rank=None, gather=None):
     if a.pack and os.path.exists(a.pack) and gather is None:
         return pack.load_products(a.pack)
     kw = {}
+    if a.eig_threshold > 0 and a.coarse == "geneo":
+        kw.update(eig_threshold=a.eig_threshold, nev_max=a.nev_max)
     if a.eigensolver == "gpu" and a.coarse == "geneo":
         kw.update(eigensolver="gpu", eig_device=int(os.environ.get("LOCAL_RANK", 0)))
     if gather is not None:
