@@ -3,6 +3,7 @@
 // apply path and the device-resident PCG loop.  No CPU compute path exists behind these entry points.
 #include "../../include/ddm_b200.h"
 #include "trisolve.cuh"
+#include "factorize.cuh"
 
 #include <cooperative_groups.h>
 #include <cuda_runtime.h>
@@ -169,6 +170,9 @@ struct ddm_ctx {
     int *cnt = nullptr; // [2*nsn + 2]: fwd counters, bwd counters, tickets
     int tri_grid = 0;
     cublasHandle_t blas = nullptr;
+    cusolverDnHandle_t solver = nullptr;
+    double *mf_arena = nullptr;  // update matrices of the device factorisation (setup scratch, released by ddm_finalize)
+    int64_t mf_arena_doubles = 0;
     // reductions / scalars
     int nred = 0;
     double *partial = nullptr, *scal = nullptr; // scal[8] device scalars
@@ -307,6 +311,8 @@ extern "C" int ddm_ctx_destroy(ddm_ctx *c)
     }
     if (c->comm) g_nccl.CommDestroy(c->comm);
     if (c->blas) cublasDestroy(c->blas);
+    if (c->solver) cusolverDnDestroy(c->solver);
+    cudaFree(c->mf_arena);
     if (c->sw0) {
         cudaEventDestroy(c->sw0);
         cudaEventDestroy(c->sw1);
@@ -503,30 +509,14 @@ static inline int64_t diag_tile_off(int32_t cw, int32_t c)
     return off;
 }
 
-// Inverse of a cw x cw lower-triangular block stored in the first cw rows of a column-major panel with leading dimension m;
-// out(i, j) at out[j*cw + i].  Returns false on a zero pivot.
-static bool inv_lower(const double *Pn, int64_t m, int cw, double *out)
-{
-    auto Lkk = [&](int a, int b) { return Pn[(int64_t)b * m + a]; };
-    for (int j = 0; j < cw; ++j) {
-        const double djj = Lkk(j, j);
-        if (djj == 0.0 || !std::isfinite(djj)) return false;
-        out[(int64_t)j * cw + j] = 1.0 / djj;
-        for (int i = j + 1; i < cw; ++i) {
-            double acc = 0.0;
-            for (int k = j; k < i; ++k) acc += Lkk(i, k) * out[(int64_t)j * cw + k];
-            out[(int64_t)j * cw + i] = -acc / Lkk(i, i);
-        }
-    }
-    return true;
-}
-
 // x: panels of L (LL^T: the Cholesky factor; LU: unit lower L with its diagonal stored), xu: NULL for LL^T, else the panels
 // of U^T in the same layout.  Block form used by the sweeps:  A = Lt D Ut,  Lt_below = L_below L_JJ^{-1},
 // Ut_below^T = U_below^T U_JJ^{-T},  D_J = L_JJ U_JJ  (U = L^T in the symmetric case).
-static int upload_factor_impl(ddm_ctx *c, int32_t sub, int32_t n, int32_t nsuper, const int32_t *super, const int64_t *pi,
-                              const int64_t *px, const int32_t *s, const double *x, const double *xu, const int32_t *perm)
+// raw / rawU: the panels ON THE DEVICE (modified in place by the wide-supernode pass, freed by the caller).
+static int convert_factor(ddm_ctx *c, int32_t sub, int32_t n, int32_t nsuper, const int32_t *super, const int64_t *pi,
+                          const int64_t *px, const int32_t *s, double *raw, double *rawU, const int32_t *perm)
 {
+    const bool have_u = rawU != nullptr;
     CU(cudaSetDevice(c->device));
     if (sub < 0 || sub >= c->nsub) return fail("factor for subdomain %d, but %d are hosted", sub, c->nsub);
     if (n != c->sub_ptr[sub + 1] - c->sub_ptr[sub]) return fail("factor size %d != subdomain size %lld", n, (long long)(c->sub_ptr[sub + 1] - c->sub_ptr[sub]));
@@ -543,7 +533,7 @@ static int upload_factor_impl(ddm_ctx *c, int32_t sub, int32_t n, int32_t nsuper
     mix(pi, sizeof(int64_t) * (nsuper + 1));
     mix(s, sizeof(int32_t) * pi[nsuper]);
     mix(perm, sizeof(int32_t) * n);
-    const bool same = F.present && F.sig == sig && F.lu == (xu != nullptr);
+    const bool same = F.present && F.sig == sig && F.lu == have_u;
     double *keep_panel = nullptr, *keep_panelU = nullptr;
     int32_t *keep_rowidx = nullptr;
     if (same) {
@@ -557,7 +547,7 @@ static int upload_factor_impl(ddm_ctx *c, int32_t sub, int32_t n, int32_t nsuper
     F.sig = sig;
     F.rowidx = keep_rowidx;
     F.n = n;
-    F.lu = xu != nullptr;
+    F.lu = have_u;
     const bool lu = F.lu;
     F.ubelow_off.assign(nsuper, 0);
     int64_t utile_doubles = 0;
@@ -570,7 +560,6 @@ static int upload_factor_impl(ddm_ctx *c, int32_t sub, int32_t n, int32_t nsuper
     F.row_off.resize(nsuper);
     std::vector<int32_t> col2super(n, -1);
     std::vector<ConvTile> conv, convU;
-    std::vector<double> aux;  // small supernodes: Linv and Dinv blocks; wide supernodes: device-side work space behind it
     int64_t tile_doubles = 0, nrows_tot = 0, aux_wide = 0;
     struct Wide {
         int32_t J;
@@ -603,32 +592,22 @@ static int upload_factor_impl(ddm_ctx *c, int32_t sub, int32_t n, int32_t nsuper
         if (lu) utile_doubles += (int64_t)Rb * 32 * cw;
         nrows_tot += (int64_t)(Rd + Rb) * 32;
     }
-    // aux layout: per small supernode [Linv | Dinv | (LU) Tinv, T = U_JJ^T], then the wide supernodes' work space
+    // aux layout: per small supernode [Linv | Dinv | (LU) Tinv, T = U_JJ^T], then the wide supernodes' work space;
+    // the small inverses are computed on the device (mf_small_inverse_kernel) from the raw panels
     std::vector<int64_t> linv_off(nsuper, -1), dinv_off(nsuper, -1), tinv_off(nsuper, -1);
+    std::vector<SmallInv> small;
+    int64_t aux_small_doubles = 0;
     for (int32_t J = 0; J < nsuper; ++J) {
         const int32_t cw = F.cw[J];
         if (cw > 32) continue;
-        const int64_t m = pi[J + 1] - pi[J];
-        const int64_t lo = (int64_t)aux.size();
-        aux.resize(lo + (lu ? 3 : 2) * (size_t)cw * cw, 0.0);
-        double *Li = aux.data() + lo, *Di = Li + (size_t)cw * cw, *Ti = lu ? Di + (size_t)cw * cw : Li;
+        const int64_t lo = aux_small_doubles;
+        aux_small_doubles += (lu ? 3 : 2) * (int64_t)cw * cw;
         linv_off[J] = lo;
         dinv_off[J] = lo + (int64_t)cw * cw;
         if (lu) tinv_off[J] = lo + 2 * (int64_t)cw * cw;
-        if (!inv_lower(x + px[J], m, cw, Li) || (lu && !inv_lower(xu + px[J], m, cw, Ti)))
-            return fail("factor of subdomain %d has a zero pivot", sub);
-        if (!lu)
-            for (int j = 0; j < cw; ++j)
-                if (!(x[px[J] + (int64_t)j * m + j] > 0.0)) return fail("factor of subdomain %d has a non-positive pivot", sub);
-        // D^{-1} = U_JJ^{-1} L_JJ^{-1} = Tinv^T Linv:  Dinv(a, b) = sum_{k >= max(a,b)} Tinv(k, a) Linv(k, b)
-        for (int a = 0; a < cw; ++a)
-            for (int b = 0; b < cw; ++b) {
-                double acc = 0.0;
-                for (int k = std::max(a, b); k < cw; ++k) acc += Ti[(int64_t)a * cw + k] * Li[(int64_t)b * cw + k];
-                Di[(size_t)b * cw + a] = acc;
-            }
+        small.push_back({px[J], linv_off[J], dinv_off[J], lu ? tinv_off[J] : -1, (int32_t)(pi[J + 1] - pi[J]), cw});
     }
-    const int64_t aux_small = (int64_t)aux.size();
+    const int64_t aux_small = aux_small_doubles;
     for (int32_t J = 0; J < nsuper; ++J) {
         const int32_t cw = F.cw[J];
         if (cw <= 32) continue;
@@ -696,12 +675,17 @@ static int upload_factor_impl(ddm_ctx *c, int32_t sub, int32_t n, int32_t nsuper
         if (F.parent[J] >= 0) F.level[F.parent[J]] = std::max(F.level[F.parent[J]], F.level[J] + 1);
     F.panel_doubles = tile_doubles;
     // device: raw panels + aux -> tiles
-    double *raw = nullptr, *rawU = nullptr, *daux = nullptr;
+    double *daux = nullptr;
     ConvTile *dconv = nullptr, *dconvU = nullptr;
-    CK(dev_upload(&raw, x, (size_t)px[nsuper]));
-    if (lu) CK(dev_upload(&rawU, xu, (size_t)px[nsuper]));
+    SmallInv *dsmall = nullptr;
+    int *derr = nullptr;
     CU(cudaMalloc((void **)&daux, sizeof(double) * std::max<int64_t>(1, aux_small + aux_wide)));
-    if (aux_small) CU(cudaMemcpy(daux, aux.data(), sizeof(double) * aux_small, cudaMemcpyHostToDevice));
+    CU(cudaMalloc((void **)&derr, sizeof(int)));
+    CU(cudaMemsetAsync(derr, 0, sizeof(int), c->s));
+    if (!small.empty()) {
+        CK(dev_upload(&dsmall, small.data(), small.size()));
+        LAUNCH(c, mf_small_inverse_kernel, (int)small.size(), 32, (int32_t)small.size(), dsmall, raw, rawU, daux, lu ? 1 : 0, derr);
+    }
     if (!wide.empty()) {
         if (!c->blas) {
             if (cublasCreate(&c->blas) != CUBLAS_STATUS_SUCCESS) return fail("cublasCreate failed");
@@ -752,16 +736,36 @@ static int upload_factor_impl(ddm_ctx *c, int32_t sub, int32_t n, int32_t nsuper
             LAUNCH(c, convert_tiles_kernel, nblocks(nt * 32), 256, nt, dconvU, rawU, daux, F.panelU);
         }
     }
+    int herr = 0;
+    CU(cudaMemcpyAsync(&herr, derr, sizeof(int), cudaMemcpyDeviceToHost, c->s));
     CU(cudaStreamSynchronize(c->s));
     CU(cudaGetLastError());
-    cudaFree(raw);
-    cudaFree(rawU);
     cudaFree(daux);
     cudaFree(dconv);
     cudaFree(dconvU);
+    cudaFree(dsmall);
+    cudaFree(derr);
+    if (herr) {
+        c->finalized = false;
+        return fail(lu ? "factor of subdomain %d has a zero pivot" : "factor of subdomain %d has a non-positive pivot", sub);
+    }
     F.present = true;
     if (!same) c->finalized = false;
     return 0;
+}
+
+// Host panels -> device, then the conversion above.
+static int upload_factor_impl(ddm_ctx *c, int32_t sub, int32_t n, int32_t nsuper, const int32_t *super, const int64_t *pi,
+                              const int64_t *px, const int32_t *s, const double *x, const double *xu, const int32_t *perm)
+{
+    CU(cudaSetDevice(c->device));
+    double *raw = nullptr, *rawU = nullptr;
+    CK(dev_upload(&raw, x, (size_t)px[nsuper]));
+    int rc = xu ? dev_upload(&rawU, xu, (size_t)px[nsuper]) : 0;
+    if (!rc) rc = convert_factor(c, sub, n, nsuper, super, pi, px, s, raw, rawU, perm);
+    cudaFree(raw);
+    cudaFree(rawU);
+    return rc;
 }
 
 extern "C" int ddm_upload_factor(ddm_ctx *c, int32_t sub, int32_t n, int32_t nsuper, const int32_t *super, const int64_t *pi,
@@ -774,6 +778,232 @@ extern "C" int ddm_upload_factor_lu(ddm_ctx *c, int32_t sub, int32_t n, int32_t 
 {
     if (!xu) return fail("ddm_upload_factor_lu needs the U panels");
     return upload_factor_impl(c, sub, n, nsuper, super, pi, px, s, xl, xu, perm);
+}
+
+// ------------------------------------------------------------------------------------------------ device factorisation
+// First-fit allocator (host bookkeeping only) for the update matrices of the multifrontal factorisation: a front's update
+// matrix lives from its own level until its parent's level has been processed.
+namespace {
+struct ArenaPlan {
+    std::map<int64_t, int64_t> free_;  // offset -> length
+    int64_t top = 0;
+    int64_t alloc(int64_t len)
+    {
+        for (auto it = free_.begin(); it != free_.end(); ++it)
+            if (it->second >= len) {
+                const int64_t off = it->first, rest = it->second - len;
+                free_.erase(it);
+                if (rest) free_[off + len] = rest;
+                return off;
+            }
+        // grow at the top (merge with a free block that ends there)
+        if (!free_.empty()) {
+            auto last = std::prev(free_.end());
+            if (last->first + last->second == top) {
+                const int64_t off = last->first;
+                free_.erase(last);
+                top = off + len;
+                return off;
+            }
+        }
+        const int64_t off = top;
+        top += len;
+        return off;
+    }
+    void release(int64_t off, int64_t len)
+    {
+        auto nx = free_.lower_bound(off);
+        if (nx != free_.begin()) {
+            auto pv = std::prev(nx);
+            if (pv->first + pv->second == off) {
+                off = pv->first;
+                len += pv->second;
+                free_.erase(pv);
+            }
+        }
+        if (nx != free_.end() && off + len == nx->first) {
+            len += nx->second;
+            free_.erase(nx);
+        }
+        free_[off] = len;
+    }
+};
+struct DevGuard {  // frees the temporaries of a setup routine on every return path
+    std::vector<void *> ptrs;
+    ~DevGuard()
+    {
+        for (void *p : ptrs) cudaFree(p);
+    }
+    void own(const void *p) { ptrs.push_back(const_cast<void *>(p)); }
+};
+}  // namespace
+
+// Numeric supernodal Cholesky on the device (factorize.cuh) followed by the tile conversion.  Symbolic arrays as in
+// ddm_upload_factor; (a_rowptr, a_col, a_val): A_i in CSR, the subdomain's own numbering, both triangles stored.
+extern "C" int ddm_factorize_subdomain(ddm_ctx *c, int32_t sub, int32_t n, int32_t nsuper, const int32_t *super, const int64_t *pi,
+                                       const int64_t *px, const int32_t *s, const int32_t *perm, const int64_t *a_rowptr,
+                                       const int32_t *a_col, const double *a_val, double *x_out)
+{
+    CU(cudaSetDevice(c->device));
+    if (sub < 0 || sub >= c->nsub) return fail("factorisation for subdomain %d, but %d are hosted", sub, c->nsub);
+    if (n != c->sub_ptr[sub + 1] - c->sub_ptr[sub]) return fail("matrix size %d != subdomain size %lld", n, (long long)(c->sub_ptr[sub + 1] - c->sub_ptr[sub]));
+    if (nsuper <= 0 || super[0] != 0 || super[nsuper] != n) return fail("factorisation of subdomain %d: malformed supernode partition", sub);
+    // ---- host: tree, levels, children, arena plan
+    std::vector<int32_t> col2super(n), iperm(n, -1), parent(nsuper, -1), level(nsuper, 0);
+    for (int32_t k = 0; k < n; ++k) {
+        if (perm[k] < 0 || perm[k] >= n || iperm[perm[k]] != -1) return fail("factorisation of subdomain %d: perm is not a permutation", sub);
+        iperm[perm[k]] = k;
+    }
+    std::vector<MfFront> fr(nsuper);
+    for (int32_t J = 0; J < nsuper; ++J) {
+        const int32_t f = super[J], cw = super[J + 1] - f;
+        const int64_t m = pi[J + 1] - pi[J];
+        if (cw <= 0 || m < cw || m > INT32_MAX) return fail("factorisation of subdomain %d: malformed supernode %d", sub, J);
+        for (int32_t j = 0; j < cw; ++j) col2super[f + j] = J;
+        fr[J] = MfFront{px[J], pi[J], -1, f, cw, (int32_t)m, 0, 0, 0};
+    }
+    for (int32_t J = 0; J < nsuper; ++J)
+        if (fr[J].m > fr[J].cw) {
+            parent[J] = col2super[s[pi[J] + fr[J].cw]];
+            if (parent[J] <= J) return fail("factorisation of subdomain %d: supernodes are not in elimination order", sub);
+        }
+    int32_t nlevel = 1;
+    for (int32_t J = 0; J < nsuper; ++J)
+        if (parent[J] >= 0) {
+            level[parent[J]] = std::max(level[parent[J]], level[J] + 1);
+            nlevel = std::max(nlevel, level[parent[J]] + 1);
+        }
+    std::vector<int32_t> child_cnt(nsuper + 1, 0), child_idx(std::max(nsuper, 1));
+    for (int32_t J = 0; J < nsuper; ++J)
+        if (parent[J] >= 0) child_cnt[parent[J] + 1]++;
+    for (int32_t J = 0; J < nsuper; ++J) child_cnt[J + 1] += child_cnt[J];
+    {
+        std::vector<int32_t> fill(child_cnt.begin(), child_cnt.end() - 1);
+        for (int32_t J = 0; J < nsuper; ++J)
+            if (parent[J] >= 0) child_idx[fill[parent[J]]++] = J;  // ascending child index: fixed summation order
+    }
+    std::vector<std::vector<int32_t>> by_level(nlevel);
+    for (int32_t J = 0; J < nsuper; ++J) by_level[level[J]].push_back(J);
+    ArenaPlan plan;
+    for (int32_t l = 0; l < nlevel; ++l) {
+        for (int32_t J : by_level[l]) {
+            fr[J].child_ptr = child_cnt[J];
+            fr[J].child_end = child_cnt[J + 1];
+            const int64_t nb = fr[J].m - fr[J].cw;
+            if (parent[J] >= 0) fr[J].uoff = plan.alloc(nb * nb);
+        }
+        for (int32_t J : by_level[l])
+            for (int32_t q = child_cnt[J]; q < child_cnt[J + 1]; ++q) {
+                const int32_t ch = child_idx[q];
+                const int64_t nb = fr[ch].m - fr[ch].cw;
+                plan.release(fr[ch].uoff, nb * nb);
+            }
+    }
+    // small fronts of all levels in one list (level by level), wide ones handled one by one
+    std::vector<int32_t> small_list, small_ptr(nlevel + 1, 0);
+    int32_t max_cw = 0;
+    for (int32_t l = 0; l < nlevel; ++l) {
+        for (int32_t J : by_level[l])
+            if (fr[J].cw <= 32) small_list.push_back(J);
+            else max_cw = std::max(max_cw, fr[J].cw);
+        small_ptr[l + 1] = (int32_t)small_list.size();
+    }
+    // ---- device
+    DevGuard guard;
+    const int64_t nnzA = a_rowptr[n];
+    double *raw = nullptr, *d_val = nullptr, *work = nullptr;
+    int64_t *d_rowptr = nullptr;
+    int32_t *d_col = nullptr, *d_iperm = nullptr, *d_c2s = nullptr, *d_s = nullptr, *d_rel = nullptr, *d_parent = nullptr, *d_child = nullptr, *d_small = nullptr;
+    MfFront *d_fr = nullptr;
+    int *d_err = nullptr, *d_info = nullptr;
+    CU(cudaMalloc((void **)&raw, sizeof(double) * std::max<int64_t>(1, px[nsuper])));
+    guard.own(raw);
+    CU(cudaMemsetAsync(raw, 0, sizeof(double) * px[nsuper], c->s));
+    if (c->mf_arena_doubles < plan.top) {
+        cudaFree(c->mf_arena);
+        c->mf_arena = nullptr;
+        c->mf_arena_doubles = 0;
+        CU(cudaMalloc((void **)&c->mf_arena, sizeof(double) * std::max<int64_t>(1, plan.top)));
+        c->mf_arena_doubles = plan.top;
+    }
+    double *arena = c->mf_arena;
+#define UP(dst, src, cnt)          \
+    CK(dev_upload(&dst, src, cnt)); \
+    guard.own(dst);
+    UP(d_rowptr, a_rowptr, (size_t)n + 1)
+    UP(d_col, a_col, (size_t)nnzA)
+    UP(d_val, a_val, (size_t)nnzA)
+    UP(d_iperm, iperm.data(), (size_t)n)
+    UP(d_c2s, col2super.data(), (size_t)n)
+    UP(d_s, s, (size_t)pi[nsuper])
+    UP(d_parent, parent.data(), (size_t)nsuper)
+    UP(d_child, child_idx.data(), child_idx.size())
+    UP(d_small, small_list.data(), small_list.size())
+    UP(d_fr, fr.data(), (size_t)nsuper)
+#undef UP
+    CU(cudaMalloc((void **)&d_rel, sizeof(int32_t) * std::max<int64_t>(1, pi[nsuper])));
+    guard.own(d_rel);
+    CU(cudaMalloc((void **)&d_err, sizeof(int) * 2));
+    guard.own(d_err);
+    CU(cudaMemsetAsync(d_err, 0, sizeof(int) * 2, c->s));
+    d_info = d_err + 1;
+    LAUNCH(c, mf_scatter_kernel, nblocks((int64_t)n * 32), 256, n, d_rowptr, d_col, d_val, d_iperm, d_c2s, d_fr, d_s, raw, d_err);
+    LAUNCH(c, mf_relidx_kernel, nsuper, 128, nsuper, d_fr, d_parent, d_s, d_rel);
+    int lwork = 0;
+    if (max_cw > 0) {
+        if (!c->blas) {
+            if (cublasCreate(&c->blas) != CUBLAS_STATUS_SUCCESS) return fail("cublasCreate failed");
+            cublasSetStream(c->blas, c->s);
+        }
+        if (!c->solver) {
+            if (cusolverDnCreate(&c->solver) != CUSOLVER_STATUS_SUCCESS) return fail("cusolverDnCreate failed");
+            cusolverDnSetStream(c->solver, c->s);
+        }
+        for (int32_t J = 0; J < nsuper; ++J)
+            if (fr[J].cw > 32) {
+                int lw = 0;
+                if (cusolverDnDpotrf_bufferSize(c->solver, CUBLAS_FILL_MODE_LOWER, fr[J].cw, raw + fr[J].px, fr[J].m, &lw) != CUSOLVER_STATUS_SUCCESS)
+                    return fail("cusolverDnDpotrf_bufferSize failed");
+                lwork = std::max(lwork, lw);
+            }
+        CU(cudaMalloc((void **)&work, sizeof(double) * std::max(1, lwork)));
+        guard.own(work);
+    }
+    const double one = 1.0, mone = -1.0;
+    for (int32_t l = 0; l < nlevel; ++l) {
+        const int32_t ns = small_ptr[l + 1] - small_ptr[l];
+        if (ns > 0) LAUNCH(c, mf_small_fronts_kernel, ns, 256, d_fr, d_small + small_ptr[l], d_child, d_rel, raw, arena, d_err);
+        for (int32_t J : by_level[l]) {
+            const MfFront &F = fr[J];
+            if (F.cw <= 32) continue;
+            const int32_t nb = F.m - F.cw;
+            if (F.uoff >= 0) CU(cudaMemsetAsync(arena + F.uoff, 0, sizeof(double) * (size_t)nb * nb, c->s));
+            for (int32_t q = F.child_ptr; q < F.child_end; ++q) {
+                const int32_t ch = child_idx[q];
+                const int32_t nbc = fr[ch].m - fr[ch].cw;
+                LAUNCH(c, mf_extend_add_kernel, std::min(nblocks((int64_t)nbc * 32), c->sm_count * 8), 256, d_fr, J, ch, d_rel, raw, arena);
+            }
+            double *L11 = raw + F.px;
+            if (cusolverDnDpotrf(c->solver, CUBLAS_FILL_MODE_LOWER, F.cw, L11, F.m, work, lwork, d_info) != CUSOLVER_STATUS_SUCCESS)
+                return fail("cusolverDnDpotrf failed");
+            LAUNCH(c, mf_collect_info_kernel, 1, 32, d_info, d_err);
+            if (nb > 0) {
+                if (cublasDtrsm(c->blas, CUBLAS_SIDE_RIGHT, CUBLAS_FILL_MODE_LOWER, CUBLAS_OP_T, CUBLAS_DIAG_NON_UNIT, nb, F.cw, &one, L11, F.m, L11 + F.cw, F.m) != CUBLAS_STATUS_SUCCESS)
+                    return fail("cublasDtrsm (L21) failed");
+                if (F.uoff >= 0 &&
+                    cublasDsyrk(c->blas, CUBLAS_FILL_MODE_LOWER, CUBLAS_OP_N, nb, F.cw, &mone, L11 + F.cw, F.m, &one, arena + F.uoff, nb) != CUBLAS_STATUS_SUCCESS)
+                    return fail("cublasDsyrk failed");
+            }
+        }
+    }
+    int herr = 0;
+    CU(cudaMemcpyAsync(&herr, d_err, sizeof(int), cudaMemcpyDeviceToHost, c->s));
+    CU(cudaStreamSynchronize(c->s));
+    CU(cudaGetLastError());
+    if (herr == 1) return fail("factorisation of subdomain %d: a matrix entry lies outside the symbolic structure", sub);
+    if (herr) return fail("factorisation of subdomain %d: matrix is not positive definite", sub);
+    if (x_out) CU(cudaMemcpy(x_out, raw, sizeof(double) * px[nsuper], cudaMemcpyDeviceToHost));
+    return convert_factor(c, sub, n, nsuper, super, pi, px, s, raw, nullptr, perm);
 }
 
 // A0 (device, row-major, c->A0) -> explicit inverse c->A0inv; A0 points to a host copy (symmetry test).

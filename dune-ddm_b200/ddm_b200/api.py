@@ -141,6 +141,9 @@ class Context:
         lib = self.lib
         for i in range(a, b):
             F = P.factors[i]
+            if hasattr(F, "an"):  # factor.PendingFactor: numeric phase on the device, with the host's symbolic analysis
+                self.factorize(i - a, F)
+                continue
             if hasattr(F, "xu"):  # non-symmetric subdomain matrix: LU factor (the reference's UMFPack branch, schwarz.hh:85-92)
                 check(lib.ddm_upload_factor_lu(self.h, C.c_int32(i - a), C.c_int32(F.n), C.c_int32(F.nsuper),
                                                _p(np.ascontiguousarray(F.super_, dtype=np.int32), C.c_int32),
@@ -158,6 +161,20 @@ class Context:
                                         _p(np.ascontiguousarray(F.s, dtype=np.int32), C.c_int32),
                                         _p(np.ascontiguousarray(F.x, dtype=np.float64), C.c_double),
                                         _p(np.ascontiguousarray(F.perm, dtype=np.int32), C.c_int32)))
+
+    def factorize(self, sub, F, want_panels=False):
+        """ddm_factorize_subdomain for local subdomain `sub`: F = factor.PendingFactor (analysis + A_i).  want_panels: also
+        return the LL^T panels in cholmod layout (the array ddm_upload_factor would have taken)."""
+        an, A = F.an, F.A
+        x = np.empty(int(an.px[-1])) if want_panels else None
+        check(self.lib.ddm_factorize_subdomain(
+            self.h, C.c_int32(sub), C.c_int32(an.n), C.c_int32(an.first.size - 1),
+            _p(np.ascontiguousarray(an.first, dtype=np.int32), C.c_int32), _p(np.ascontiguousarray(an.pi, dtype=np.int64), C.c_int64),
+            _p(np.ascontiguousarray(an.px, dtype=np.int64), C.c_int64), _p(an.row_lists(), C.c_int32),
+            _p(np.ascontiguousarray(an.perm, dtype=np.int32), C.c_int32), _p(np.ascontiguousarray(A.indptr, dtype=np.int64), C.c_int64),
+            _p(np.ascontiguousarray(A.indices, dtype=np.int32), C.c_int32), _p(np.ascontiguousarray(A.data, dtype=np.float64), C.c_double),
+            _p(x, C.c_double) if want_panels else None))
+        return x
 
     # -- helpers
     def vector(self, values=None):

@@ -184,6 +184,50 @@ class Analysis:
     c_src: np.ndarray | None = None
 
 
+    def row_lists(self):
+        """cholmod's L->s: per supernode its own columns, then its row structure (pivot numbering)."""
+        if getattr(self, "_s", None) is None:
+            s = np.empty(self.pi[-1], dtype=np.int32)
+            for J in range(self.first.size - 1):
+                f, l = int(self.first[J]), int(self.first[J + 1])
+                s[self.pi[J] : self.pi[J] + (l - f)] = np.arange(f, l)
+                s[self.pi[J] + (l - f) : self.pi[J + 1]] = self.structs[J]
+            self._s = s
+        return self._s
+
+    def nnz_lower(self):
+        c = np.diff(self.first).astype(np.int64)
+        r = np.diff(self.pi) - c
+        return int((c * (c + 1) // 2 + r * c).sum())
+
+
+@dataclass
+class PendingFactor:
+    """A subdomain matrix with its symbolic analysis, numeric phase still to be done: on the device by
+    ddm_factorize_subdomain (api.Context.upload_factors), or on the host by .host() (what the CPU oracle uses)."""
+
+    an: Analysis
+    A: sp.csr_matrix  # A_i, the pattern that was analysed
+
+    @property
+    def n(self):
+        return self.an.n
+
+    @property
+    def perm(self):
+        return self.an.perm
+
+    @property
+    def nsuper(self):
+        return self.an.first.size - 1
+
+    def nnz_lower(self):
+        return self.an.nnz_lower()
+
+    def host(self):
+        return numeric_cholesky(self.an, self.A.data)
+
+
 def _structures(first, indptr, indices):
     """struct(J) = (adj(J) u children's struct) \\ {<= last column of J}; parent = supernode of the first row below."""
     nsuper = first.size - 1

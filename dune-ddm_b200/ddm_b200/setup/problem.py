@@ -93,7 +93,10 @@ def _sub_job(i):
         Ai = A[s][:, s].tocsr()
         Ai.sort_indices()
         co = g["coords"][s] if g["coords"] is not None else None
-        F = factor.cholesky_supernodal(Ai, co, g["leaf_size"]) if g["symmetric"] else factor.lu_supernodal(Ai, co, g["leaf_size"])
+        if g["numeric"] == "device" and g["symmetric"]:  # symbolic analysis here, numeric phase by ddm_factorize_subdomain at upload
+            F = factor.PendingFactor(factor.analyse(Ai, co, g["leaf_size"], symmetric=True), Ai)
+        else:
+            F = factor.cholesky_supernodal(Ai, co, g["leaf_size"]) if g["symmetric"] else factor.lu_supernodal(Ai, co, g["leaf_size"])
         kind = g["coarse"]
         dl = g["dirichlet"][s]
         if kind == "geneo":
@@ -120,7 +123,7 @@ def _sub_job(i):
 
 def build(coords, cells, Ke, dirichlet, rhs, cell_part, nsub, overlap=2, pou_kind="distance", shrink=0,
           coarse="geneo", nev=16, shift=1e-3, eig_tol=1e-5, leaf_size=32, workers=None, meta=None, only=None, gather=None,
-          A_full=None, symmetric=True, ke_fn=None, eigensolver="host", eig_device=0, eig_threshold=-0.5, nev_max=None):
+          A_full=None, symmetric=True, ke_fn=None, eigensolver="host", eig_device=0, eig_threshold=-0.5, nev_max=None, numeric="host"):
     """Generic pipeline from an element-wise description to SetupProducts.
 
     only / gather: with several processes (one per GPU) every process factors and builds the coarse basis of its own
@@ -176,7 +179,7 @@ def build(coords, cells, Ke, dirichlet, rhs, cell_part, nsub, overlap=2, pou_kin
     _G.clear()
     _G.update(A=A, subs=subs, coords=coords, cells=cells, Ke=Ke, dirichlet=dirichlet, shared=shared, pou=pou,
               coarse=coarse, nev=nev, shift=shift, eig_tol=eig_tol, leaf_size=leaf_size, symmetric=symmetric,
-              eigensolver=eigensolver if coarse == "geneo" else "host", eig_threshold=eig_threshold, nev_max=nev_max)
+              eigensolver=eigensolver if coarse == "geneo" else "host", eig_threshold=eig_threshold, nev_max=nev_max, numeric=numeric)
     workers = workers or min(max(len(todo), 1), os.cpu_count() or 1)
     factors = [None] * nsub
     Z = [None] * nsub

@@ -105,6 +105,18 @@ int ddm_upload_factor(ddm_ctx *ctx, int32_t sub, int32_t n, int32_t nsuper, cons
 int ddm_upload_factor_lu(ddm_ctx *ctx, int32_t sub, int32_t n, int32_t nsuper, const int32_t *super, const int64_t *pi,
                          const int64_t *px, const int32_t *s, const double *xl, const double *xu, const int32_t *perm);
 
+/* Numeric factorisation of A_i on the device with a given symbolic analysis, then the same re-layout as
+ * ddm_upload_factor: the cholmod_l_factorize half of Dune::Cholmod::setMatrix
+ * (extern/dune-istl/dune/istl/cholmod.hh:469-472; the cholmod_l_analyze half -- perm, super, pi, px, s -- stays with the
+ * caller), and the numeric re-factorisation of TwoLevelSchwarzSolver's update branch (dune/ddm/twolevel_schwarz.hh:99-104).
+ * (a_rowptr, a_col, a_val): A_i = R_i A R_i^T in CSR, the subdomain's own numbering, symmetric positive definite, both
+ * triangles stored, every entry inside the symbolic structure.  x_out (may be NULL) receives the LL^T panels in
+ * cholmod_factor layout (px[nsuper] doubles), i.e. what ddm_upload_factor would have been given.  Setup only: multifrontal,
+ * level by level; cuSOLVER/cuBLAS for the wide fronts. */
+int ddm_factorize_subdomain(ddm_ctx *ctx, int32_t sub, int32_t n, int32_t nsuper, const int32_t *super, const int64_t *pi,
+                            const int64_t *px, const int32_t *s, const int32_t *perm, const int64_t *a_rowptr,
+                            const int32_t *a_col, const double *a_val, double *x_out);
+
 /* Coarse space (dune/ddm/galerkin_preconditioner.hh:119-144,220-349): per hosted subdomain k[i]
  * basis vectors, Z = concatenation of column-major n_i x k[i] blocks (restr_vecs, :353), the
  * global coarse dimension N0, this context's first coarse index k_offset, and the dense
