@@ -20,11 +20,14 @@ import scipy.sparse as sp
 import scipy.sparse.linalg as spla
 
 
-def neumann_matrices(n, cells, Ke, sub, shared_count, dirichlet):
+def neumann_matrices(n, cells, Ke, sub, shared_count, dirichlet, cand=None):
     """A_neu (elements inside the subdomain) and B_neu (elements inside its overlap region),
-    both in the subdomain's local numbering, Dirichlet rows/cols eliminated."""
+    both in the subdomain's local numbering, Dirichlet rows/cols eliminated.  cand: indices of the cells worth looking at
+    (a superset of the cells inside the subdomain; default all) -- Ke is indexed with cell indices or a mask over all cells."""
     loc = -np.ones(n, dtype=np.int64)
     loc[sub] = np.arange(sub.size)
+    if cand is not None:
+        cells = cells[cand]
     lc = loc[cells]
     inside = (lc >= 0).all(axis=1)
     ovl_node = np.zeros(n, dtype=bool)
@@ -36,7 +39,7 @@ def neumann_matrices(n, cells, Ke, sub, shared_count, dirichlet):
         c = lc[sel]
         rows = np.repeat(c, k, axis=1).ravel()
         cols = np.tile(c, (1, k)).ravel()
-        M = sp.coo_matrix((Ke[sel].ravel(), (rows, cols)), shape=(sub.size, sub.size)).tocsr()
+        M = sp.coo_matrix((Ke[sel if cand is None else cand[sel]].ravel(), (rows, cols)), shape=(sub.size, sub.size)).tocsr()
         M.sum_duplicates()
         return M
 
