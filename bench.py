@@ -1,14 +1,15 @@
 #!/usr/bin/env python
 """Benchmark of the solve phase: two-level additive Schwarz PCG to 1e-8 (BASELINE.json metric).
 
-  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference] [--ncell C] [--nsub S] [--coarse geneo|pou]
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference] [--workload q1cube|p1cube] [--ncell C] [--nsub S]
 
-A step = one complete solve phase of the workload: PCG (Dune::CGSolver recurrences) preconditioned with the two-level
-additive Schwarz method, from x0 = 0 to a defect reduction of 1e-8.  The workload is BASELINE.json configs[1]
-("3D Poisson, heterogeneous coefficient, 64 subdomains, 2-level GenEO PCG") on a Kuhn-triangulated unit cube
-(the reference's data/unitcube.msh does not exist on the GPU box); with N GPUs the mesh of the same cube is refined to
-64 subdomains and ncell^3 cells per GPU (weak scaling).  Setup (mesh, assembly, factorisation, GenEO) runs on the host and is not timed, as in the reference's
-own "Total/Linear solve" event (examples/poisson.cc:171-174).
+A step = one complete solve phase of the workload: PCG (Dune::CGSolver recurrences) preconditioned with the two-level additive
+Schwarz method (GenEO coarse space), from x0 = 0 to a defect reduction of 1e-8.  Default workload = the configuration
+BASELINE.json's metric is quoted on, configs[4]: structured 3-D Q1 Poisson (27-point), channels coefficient 1e6, 4 x 4 x 4 brick
+subdomains per GPU, overlap 2, GenEO nev 16; with N GPUs the unit cube is refined by the GPU grid (weak scaling: 8 GPUs =
+8 x 8 x 8 = 512 subdomains).  Setup is not timed, as in the reference's own "Total/Linear solve" event (examples/poisson.cc:171-174):
+every process builds only its own GPU's region of the mesh (setup/local.py), numeric factorisations, GenEO eigensolves and the
+Galerkin product run on the device.  `--workload p1cube` = configs[1] (3-D P1, islands coefficient, 64 RCB subdomains).
 Prints ONE JSON line on rank 0.
 """
 import argparse
@@ -29,6 +30,7 @@ METRIC = "schwarz_pcg_solved_dofs_per_second_to_1e-8"
 UNIT = "MDOF/s"
 REDUCTION = 1e-8
 MAXIT = 500
+DEFAULT_NCELL = {"q1cube": 160, "p1cube": 112}  # q1cube: 40 cells owned per brick and axis, up to 45^3 nodes per overlapping subdomain
 
 
 def parse():
@@ -37,26 +39,29 @@ def parse():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--ncell", type=int, default=int(os.environ.get("DDM_BENCH_NCELL", 112)), help="cells per unit length")
+    ap.add_argument("--workload", default=os.environ.get("DDM_BENCH_WORKLOAD", "q1cube"), choices=["p1cube", "q1cube"],
+                    help="q1cube: BASELINE.json configs[4], the configuration the metric is quoted on (default); p1cube: configs[1]")
+    ap.add_argument("--ncell", type=int, default=int(os.environ.get("DDM_BENCH_NCELL", 0)), help="cells per axis and GPU (0: the workload's default)")
     ap.add_argument("--nsub", type=int, default=64, help="subdomains per GPU")
-    ap.add_argument("--workload", default="p1cube", choices=["p1cube", "q1cube"],
-                    help="p1cube: BASELINE.json configs[1] (default, the metric's configuration); q1cube: configs[4]'s family (structured Q1, "
-                         "27-point, channels coefficient, brick subdomains; --ncell cells per axis and GPU, nsub must be a cube)")
     ap.add_argument("--coarse", default="geneo", choices=["geneo", "pou"])
     ap.add_argument("--nev", type=int, default=16)
-    ap.add_argument("--eigensolver", default=os.environ.get("DDM_BENCH_EIGENSOLVER", "host"), choices=["host", "gpu"],
-                    help="GenEO eigenproblems (setup, untimed): per-subdomain ARPACK on the host, or the batched device Lanczos")
+    ap.add_argument("--eigensolver", default=os.environ.get("DDM_BENCH_EIGENSOLVER", "gpu"), choices=["host", "gpu"],
+                    help="GenEO eigenproblems (setup, untimed): batched device Lanczos (default) or per-subdomain ARPACK on the host")
+    ap.add_argument("--numeric", default="device", choices=["host", "device"], help="numeric factorisation of the subdomain matrices (setup, untimed)")
+    ap.add_argument("--setup", default="local", choices=["local", "global"],
+                    help="q1cube weak scaling: local = every process builds its own region only (default); global = one global mesh per process")
     ap.add_argument("--overlap", type=int, default=2)
-    ap.add_argument("--eig-threshold", type=float, default=-0.5,
-                    help="GenEO: keep the eigenvectors below this eigenvalue instead of a fixed count (eigensolver_params.hh:30; <= 0: off, the default)")
-    ap.add_argument("--nev-max", type=int, default=None, help="GenEO with --eig-threshold: upper limit of the doubling of nev (default 2 nev)")
+    ap.add_argument("--eig-threshold", type=float, default=-0.5)
+    ap.add_argument("--nev-max", type=int, default=None)
     ap.add_argument("--cpu-seconds", type=float, default=20.0, help="budget of the cpu_baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--pack", default=None, help=".ddmpack cache of the setup products: loaded if present, else built and saved")
-    ap.add_argument("--strong", action="store_true",
-                    help="strong scaling: the N = 1 problem (ncell^3 cells, nsub subdomains in total) split over the GPUs instead of a problem that grows with N")
-    ap.add_argument("--setup-only", action="store_true", help="build (and save) the setup products, then exit")
-    return ap.parse_args()
+    ap.add_argument("--pack", default=None, help=".ddmpack cache of the setup products (global setup only)")
+    ap.add_argument("--strong", action="store_true", help="strong scaling: the N = 1 problem split over the GPUs")
+    ap.add_argument("--setup-only", action="store_true")
+    a = ap.parse_args()
+    if a.ncell <= 0:
+        a.ncell = DEFAULT_NCELL[a.workload]
+    return a
 
 
 def gpu_grid(n):
@@ -98,13 +103,30 @@ def workload_name(a, world):
             f"{nsub} subdomains (RCB), overlap {a.overlap}, {a.coarse} coarse space nev {a.nev}{thr}, additive, CG 1e-8")
 
 
+def config_of(a, world, n, nsub, N0):
+    """The same dictionary in both arms (the driver compares them)."""
+    return {"workload": workload_name(a, world), "dofs": int(n), "subdomains": int(nsub), "coarse_dim": int(N0),
+            "l2_policy": "inputs larger than L2: every sweep streams all subdomain factors (GBs) once, 126 MB L2"}
+
+
+def host_cores():
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
+def use_local_setup(a):
+    return a.workload == "q1cube" and not a.strong and a.setup == "local" and not a.pack and a.eig_threshold <= 0
+
+
 def build_problem(a, world, rank=None, gather=None):
-    """rank/gather given: this process builds only its own subdomains' factors and bases (one process per GPU)."""
+    """Global setup path.  rank/gather given: this process builds only its own subdomains' factors and bases (one process per GPU)."""
     from ddm_b200.setup import fem, mesh, pack, problem
 
     if a.pack and os.path.exists(a.pack) and gather is None:
         return pack.load_products(a.pack)
-    kw = {}
+    kw = dict(numeric=a.numeric)
     if a.eig_threshold > 0 and a.coarse == "geneo":
         kw.update(eig_threshold=a.eig_threshold, nev_max=a.nev_max)
     if a.eigensolver == "gpu" and a.coarse == "geneo":
@@ -113,7 +135,9 @@ def build_problem(a, world, rank=None, gather=None):
         from ddm_b200.partition import sub_ranges
 
         s0, s1 = sub_ranges(job_shape(a, world)[1], world)[rank]
-        kw.update(only=range(s0, s1), gather=gather, workers=max(1, (os.cpu_count() or 1) // world), assemble_part=(rank, world))
+        kw.update(only=range(s0, s1), gather=gather, workers=max(1, host_cores() // world), assemble_part=(rank, world))
+    else:
+        kw.update(workers=host_cores())
     P = _build_problem(a, world, fem, mesh, problem, **kw)
     if a.pack and gather is None:
         pack.save_products(a.pack, P)
@@ -122,19 +146,22 @@ def build_problem(a, world, rank=None, gather=None):
 
 def _build_problem(a, world, fem, mesh, problem, **kw):
     if a.workload == "q1cube":
-        # config C5's family: with N GPUs the unit cube is refined by the GPU grid and every GPU hosts a p x p x p block of bricks
-        # (8x8x8 subdomains -> 2x2x2 GPU bricks of 4x4x4); CPU oracle: 28 -> 29 iterations from 1 to 8 GPUs at 32 cells per GPU axis
         shape, _ = job_shape(a, world)
         pg, g = brick_grids(a, world)
         return problem.poisson_q1_cube(shape if world > 1 else a.ncell, pg, group=g, overlap=a.overlap, coarse=a.coarse, nev=a.nev, **kw)
-    # Weak scaling = the same problem (unit cube, same coefficient) on a finer mesh with more subdomains, 64 per GPU, as the
-    # reference scales (grid.refine + one rank per subdomain).  A first version tiled the coefficient pattern over a growing
-    # box instead: with 8x8x8 subdomains the fixed nev = 16 GenEO space no longer captured all high-contrast inclusions and
-    # PCG (GPU and CPU oracle alike) stagnated near 1e-6.
     shape, nsub = job_shape(a, world)
     coords, cells = mesh.structured_simplices(shape, lengths=(1.0, 1.0, 1.0))
     return problem.poisson_simplex(coords, cells, nsub, kappa_fn=fem.kappa_islands, xmax=1.0, overlap=a.overlap,
                                    coarse=a.coarse, nev=a.nev, meta=dict(mesh=f"kuhn-{shape}"), **kw)
+
+
+def build_local(a, world, rank, device):
+    from ddm_b200.setup import local
+
+    shape, _ = job_shape(a, world)
+    pg, g = brick_grids(a, world)
+    return local.poisson_q1_cube_local(shape, pg, g, rank, overlap=a.overlap, coarse=a.coarse, nev=a.nev, workers=max(1, host_cores() // world),
+                                       numeric=a.numeric, eigensolver=a.eigensolver, eig_device=device)
 
 
 class ClockSampler:
@@ -185,58 +212,180 @@ def dist_env():
     return rank, world, local
 
 
-def cpu_baseline_sample(P, its_full, budget_s, nthreads):
-    """The oracle (CPU restatement, all host threads) on a bounded sample: the first m PCG iterations of the same
-    solve, extrapolated to the full iteration count.  oracle/ is used here only as the timed baseline."""
+def mem_available_bytes():
+    try:
+        for ln in open("/proc/meminfo"):
+            if ln.startswith("MemAvailable"):
+                return int(ln.split()[1]) * 1024
+    except OSError:
+        pass
+    return 16 << 30
+
+
+# ----------------------------------------------------------------------------- CPU arm (oracle: test infrastructure, timed here only)
+def host_products(ctx, L, subset=None):
+    """SetupProducts for the CPU oracle from one rank's local products (N = 1: the whole problem).  Subdomain factors are the
+    LL^T panels the device factorisation produced (ddm_factorize_subdomain's x_out: what ddm_upload_factor would have been
+    given), so both arms work with the same setup products; subset: keep only these subdomains (bounded sample)."""
+    import scipy.sparse as sp
+
+    from ddm_b200.setup import coarse as coarse_mod
+    from ddm_b200.setup import factor
+    from ddm_b200.setup.problem import SetupProducts
+
+    S = L.shard
+    nloc = S.n_own + S.n_ghost
+    A = sp.csr_matrix((S.val, S.col, S.rowptr), shape=(S.n_own, nloc))
+    if S.n_ghost:  # N > 1: the sample lives on this rank's shard; ghost columns are dropped (rows stay the same length: same bytes)
+        A = sp.csr_matrix((S.val, np.minimum(S.col, S.n_own - 1), S.rowptr), shape=(S.n_own, S.n_own))
+    ids = list(range(L.nsub)) if subset is None else list(subset)
+    subs, pou, Z, factors = [], [], [], []
+    for j in ids:
+        s = S.sub_dofs[S.sub_ptr[j] : S.sub_ptr[j + 1]].astype(np.int64)
+        if S.n_ghost:
+            s = np.minimum(s, S.n_own - 1)
+        subs.append(s)
+        pou.append(L.pou[j])
+        Z.append(L.Z[j])
+        F = L.factors[j]
+        if hasattr(F, "an"):
+            x = ctx.factorize(j, F, want_panels=True)
+            an = F.an
+            F = factor.SupernodalFactor(n=an.n, perm=an.perm.astype(np.int32), super_=an.first.astype(np.int32), pi=an.pi, px=an.px, s=an.row_lists(), x=x)
+        factors.append(F)
+    if subset is None and not S.n_ghost and getattr(ctx, "A0_device", None) is not None:
+        A0 = ctx.A0_device
+    else:  # sample: Galerkin matrix of the kept subdomains only
+        A0 = coarse_mod.galerkin_matrix(A, subs, Z)[0] if not S.n_ghost else np.eye(sum(z.shape[1] for z in Z))
+    b = np.zeros(S.n_own)
+    b[:] = L.b_own
+    return SetupProducts(A=A, b=b, owner=np.zeros(S.n_own, dtype=np.int32), subs=subs, pou=pou, factors=factors, Z=Z, A0=A0, meta=dict(L.meta))
+
+
+def cpu_arm(a, world, ctx, L=None, P=None, its_hint=None, budget_s=30.0, nthreads=None):
+    """Times the CPU oracle (all host threads) on the workload.  Whole problem when its factors fit in host memory (N = 1):
+    PCG itself, first m iterations, extrapolated by apply count.  Otherwise a bounded sample: the subdomain solves of a subset
+    of this rank's subdomains plus full-length vector passes, extrapolated by factor entries and by the number of GPUs' shares.
+    Returns (seconds per solve, iterations or None, description)."""
     from oracle import oracle
 
-    O = oracle.Oracle(P, nthreads=nthreads)
+    nthreads = nthreads or host_cores()
+    if P is None:
+        nnz = np.array([F.nnz_lower() for F in L.factors], dtype=np.float64)
+        panel_bytes = 8.0 * sum(float(F.an.px[-1]) if hasattr(F, "an") else float(F.x.size) for F in L.factors)
+        full = world == 1 and panel_bytes < 0.45 * mem_available_bytes()
+        if full:
+            P = host_products(ctx, L)
+    else:
+        full = True
+    if full:
+        O = oracle.Oracle(P, nthreads=nthreads)
+        t0 = time.perf_counter()
+        _, it1, _, _ = O.pcg(P.b, reduction=REDUCTION, maxit=1)
+        t1 = time.perf_counter() - t0  # 2 applies + 2 SpMV
+        if its_hint is None:  # the reference arm: one full solve for the iteration count
+            t0 = time.perf_counter()
+            _, its, conv, _ = O.pcg(P.b, reduction=REDUCTION, maxit=MAXIT)
+            t_once = time.perf_counter() - t0
+        else:
+            its, conv, t_once = int(its_hint), True, None
+        m = int(max(1, min(its, budget_s / max(t1 / 2, 1e-9))))
+        t0 = time.perf_counter()
+        _, it, _, _ = O.pcg(P.b, reduction=REDUCTION, maxit=m)
+        t = time.perf_counter() - t0
+        t_full = t * (its + 1) / (it + 1)  # it iterations cost it + 1 applies
+        desc = f"first {it} of {its} PCG iterations of the same solve ({t:.1f} s measured, extrapolated by apply count)"
+        if t_once is not None:
+            desc += f"; full solve measured once: {t_once:.1f} s"
+        return t_full, its, bool(conv), desc, O
+    # bounded sample on this rank's shard
+    budget_bytes = min(0.35 * mem_available_bytes(), 24e9)
+    order = np.argsort(-nnz)
+    pick, tot = [], 0.0
+    step = max(1, len(order) // 8)
+    for j in list(order[::step]) + list(order):
+        pb = 8.0 * float(L.factors[j].an.px[-1]) if hasattr(L.factors[j], "an") else 8.0 * L.factors[j].x.size
+        if j in pick or (pick and tot + pb > budget_bytes):
+            continue
+        pick.append(int(j))
+        tot += pb
+        if len(pick) >= max(8, nthreads):
+            break
+    Ps = host_products(ctx, L, subset=sorted(pick))
+    O = oracle.Oracle(Ps, nthreads=nthreads)
+    d = np.random.default_rng(0).standard_normal(Ps.n)
+    O.twolevel_apply(d)
+    reps, t_app = 0, 0.0
+    while t_app < budget_s / 2 and reps < 20:
+        t0 = time.perf_counter()
+        O.twolevel_apply(d)
+        t_app += time.perf_counter() - t0
+        reps += 1
+    t_app /= reps
     t0 = time.perf_counter()
-    O.pcg(P.b, reduction=REDUCTION, maxit=1)
-    t1 = time.perf_counter() - t0  # 2 applies + 2 SpMV
-    m = int(max(1, min(its_full, (budget_s - t1) / max(t1 / 2, 1e-9))))
-    t0 = time.perf_counter()
-    _, it, conv, _ = O.pcg(P.b, reduction=REDUCTION, maxit=m)
-    t = time.perf_counter() - t0
-    t_full = t * (its_full + 1) / (it + 1)  # it iterations cost it+1 applies
-    return {"value": P.n / t_full / 1e6, "unit": UNIT, "cores": nthreads, "kind": "port",
-            "sample": f"first {it} of {its_full} PCG iterations of the same solve ({t:.1f} s measured, extrapolated by apply count)",
-            "seconds_full_solve_est": t_full}
+    for _ in range(3):
+        y = O.spmv(d)
+        O.dot(d, y)
+        O.dot(d, d)
+        d2 = d + 0.5 * y
+        d2 += 0.25 * d
+    t_vec = (time.perf_counter() - t0) / 3
+    share = nnz.sum() / nnz[pick].sum()
+    t_iter = (t_app * share + t_vec) * world  # the other GPUs' shares are congruent blocks of the same cube
+    its = int(its_hint) if its_hint is not None else None
+    desc = (f"subdomain solves of {len(pick)} of {L.nsub * world} subdomains ({100 / share / world:.1f} % of the factor entries) + SpMV and vector passes of one GPU's "
+            f"share, extrapolated by factor entries and x{world} shares; {t_iter:.2f} s per PCG iteration")
+    return t_iter, its, None, desc, O
 
 
 def run_reference(a):
-    """Reference arm: the reference's CPU algorithm for the path (oracle port; the reference binary itself needs
-    MPI + SuiteSparse + Eigen, absent from this image) on all host threads, same config, metric and unit."""
-    rank, world, _ = dist_env()
+    """Reference arm: the reference's CPU algorithm for the path (oracle port; the reference binary itself needs MPI +
+    SuiteSparse + Eigen, absent from this image) on all host threads, same config, metric and unit.  The setup products are
+    made exactly as in the GPU arm (device-accelerated setup, untimed: the host-only setup does not reach this size in the
+    driver's window); the timed solve is pure CPU."""
+    rank, world, local = dist_env()
+    world = max(world, a.gpus) if world == 1 else world
     if rank != 0:
         return
-    from oracle import oracle
+    from ddm_b200 import api
 
-    P = build_problem(a, max(world, a.gpus))
-    nthreads = oracle.lib().oracle_max_threads()
-    O = oracle.Oracle(P, nthreads=nthreads)
-    t0 = time.perf_counter()
-    _, its_full, conv, hist = O.pcg(P.b, reduction=REDUCTION, maxit=MAXIT)  # full solve once: iteration count + warm-up
-    t_full_once = time.perf_counter() - t0
-    m = int(max(1, min(its_full, 30.0 / max(t_full_once / (its_full + 1), 1e-9))))
-    for _ in range(max(0, a.warmup - 1)):
-        O.pcg(P.b, reduction=REDUCTION, maxit=min(m, 2))
-    ts = []
-    for _ in range(a.steps):
-        t0 = time.perf_counter()
-        _, it, _, _ = O.pcg(P.b, reduction=REDUCTION, maxit=m)
-        ts.append((time.perf_counter() - t0) * (its_full + 1) / (it + 1))
-    t = float(np.mean(ts))
-    val = P.n / t / 1e6
+    nthreads = host_cores()
+    if use_local_setup(a):
+        L = build_local(a, world, 0, local)
+        L.k_all = np.array([z.shape[1] for z in L.Z] * world, dtype=np.int64)  # the other blocks carry the same counts (nev each)
+        n, nsub, N0 = L.n_global, L.nsub_global, int(L.k_all.sum())
+        if world == 1:
+            ctx = api.Context.from_local(L, device=local, keep_A0=True)
+        else:  # sample on rank 0's shard: no collectives, the factorisations run through a one-GPU context of the same shard
+            import copy
+
+            L1 = copy.copy(L)
+            L1.shard = copy.copy(L.shard)
+            L1.shard.world, L1.shard.rank = 1, 0
+            ctx = api.Context.from_local(L1, device=local, with_coarse=False)
+        t_solve, its, conv, desc, _ = cpu_arm(a, world, ctx, L=L, budget_s=30.0, nthreads=nthreads)
+        ctx.close()
+        if its is None:  # bounded sample: no CPU solve of the whole job exists; iteration count of this family (flat from 1 to 8 GPUs)
+            its = int(os.environ.get("DDM_BENCH_ASSUME_ITS", 30))
+            desc += f"; iteration count {its} assumed (the whole job does not fit one host: no CPU solve of it was run)"
+            t_solve = t_solve * (its + 1)
+    else:
+        P = build_problem(a, world)
+        n, nsub, N0 = P.n, P.nsub, P.A0.shape[0]
+        if any(hasattr(F, "an") for F in P.factors):
+            P.factors = [F.host() if hasattr(F, "an") else F for F in P.factors]
+        t_solve, its, conv, desc, _ = cpu_arm(a, world, None, P=P, budget_s=30.0, nthreads=nthreads)
+    val = n / t_solve / 1e6
     line = {"impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": a.gpus, "steps": a.steps, "warmup": a.warmup,
-            "ms_per_step": t * 1e3, "higher_is_better": True, "scaling": "strong" if a.strong else "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": workload_name(a, max(world, a.gpus)), "dofs": int(P.n), "iterations": int(its_full), "converged": bool(conv)},
-            "cpu_baseline": {"value": val, "unit": UNIT, "cores": nthreads, "kind": "port",
-                             "sample": f"each step = first {m} of {its_full} PCG iterations, extrapolated by apply count; full solve measured once: {t_full_once:.1f} s"},
+            "ms_per_step": t_solve * 1e3, "higher_is_better": True, "scaling": "strong" if a.strong else "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": config_of(a, world, n, nsub, N0), "iterations": int(its), "converged": conv,
+            "cpu_baseline": {"value": val, "unit": UNIT, "cores": nthreads, "kind": "port", "sample": desc,
+                             "setup": "same products as the GPU arm (device-accelerated setup, untimed); timed solve on the host cores only"},
             "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line), flush=True)
 
 
+# ----------------------------------------------------------------------------- GPU arm
 def run_b200(a):
     rank, world, local = dist_env()
     import torch
@@ -261,10 +410,20 @@ def run_b200(a):
     from ddm_b200 import api, lib
 
     t0 = time.perf_counter()
-    P = build_problem(a, world, rank, gather)
+    L = P = None
+    if use_local_setup(a):
+        L = build_local(a, world, rank, local)
+        mine = [int(z.shape[1]) for z in L.Z]
+        L.k_all = np.concatenate([np.asarray(k, dtype=np.int64) for k in (gather(mine) if world > 1 else [mine])])
+        n, nsub, N0 = L.n_global, L.nsub_global, int(L.k_all.sum())
+        nnz_r0 = sum(F.nnz_lower() for F in L.factors)
+    else:
+        P = build_problem(a, world, rank, gather)
+        n, nsub, N0 = P.n, P.nsub, P.A0.shape[0]
+        nnz_r0 = sum(F.nnz_lower() for F in P.factors if F is not None)
+    t_setup = time.perf_counter() - t0
     if rank == 0:
-        print(f"[bench] host setup {time.perf_counter() - t0:.1f} s: n={P.n} nsub={P.nsub} N0={P.A0.shape[0]} "
-              f"nnz(L) on rank 0 = {sum(F.nnz_lower() for F in P.factors if F is not None) / 1e6:.1f} M", file=sys.stderr, flush=True)
+        print(f"[bench] host setup {t_setup:.1f} s: n={n} nsub={nsub} N0={N0} nnz(L) on rank 0 = {nnz_r0 / 1e6:.1f} M", file=sys.stderr, flush=True)
     t0 = time.perf_counter()
     if world > 1:
         import ctypes as C
@@ -275,16 +434,21 @@ def run_b200(a):
         t = torch.tensor(list(buf), dtype=torch.uint8)
         dist.broadcast(t, 0)
         uid = t.tolist()
-    ctx = api.Context.from_products(P, device=local, rank=rank, world=world, unique_id=uid)
+    if L is not None:
+        ctx = api.Context.from_local(L, device=local, unique_id=uid, keep_A0=(world == 1 and not a.no_cpu_baseline))
+        b_own = L.b_own
+    else:
+        ctx = api.Context.from_products(P, device=local, rank=rank, world=world, unique_id=uid)
+        b_own = ctx.owned(P.b)
+    t_upload = time.perf_counter() - t0
     if rank == 0:
-        print(f"[bench] upload + device schedules {time.perf_counter() - t0:.1f} s", file=sys.stderr, flush=True)
+        print(f"[bench] upload, device factorisation, schedules, Galerkin product {t_upload:.1f} s", file=sys.stderr, flush=True)
     op, sp = api.NonOverlappingOperator(ctx), api.NonOverlappingScalarProduct(ctx)
     Cp = api.CombinedPreconditioner("additive")
     Cp.set_op(op)
     Cp.add(api.SchwarzPreconditioner(ctx, "standard"))
     Cp.add(api.GalerkinPreconditioner(ctx))
     cg = api.CGSolver(op, sp, Cp, reduction=REDUCTION, maxit=MAXIT)
-    b_own = ctx.owned(P.b)
     x, b = ctx.vector(), ctx.vector()
 
     def barrier():
@@ -300,7 +464,8 @@ def run_b200(a):
 
     for _ in range(a.warmup):
         res = step()
-    # ---- timed region: K solves, inputs resident in HBM, CUDA events on the library's stream
+    # ---- timed region: K solves, inputs resident in HBM, CUDA events on the library's stream.  The per-kernel event timers
+    # stay on: their events come from a pool (two cudaEventRecord per scope, nothing is created inside the solve).
     ctx.timers(True)
     l0 = ctx.launches()
     barrier()
@@ -319,8 +484,16 @@ def run_b200(a):
     timers = {ev: ctx.timer(ev) for ev in ("Schwarz/local solve fwd", "Schwarz/local solve bwd", "Schwarz/local solve", "Schwarz/get defect",
                                           "Schwarz/add solution", "GalerkinPrec/coarse solve", "CombinedPreconditioner/apply", "Operator/apply")}
     ctx.timers(False)
-    # ---- e2e: the same solve through the host-buffer entry (H2D of b and x0, D2H of x and the defect, every step)
-    bw, xw = np.empty_like(b_own), np.empty_like(b_own)  # the caller's vectors, reused across solves as a driver would
+    # ---- parity block (untimed): true residual of the last timed solve, ||b - A x|| / ||b|| over all ranks
+    r = ctx.vector(b_own)
+    bnorm = sp.norm(r)
+    op.applyscaleadd(-1.0, x, r)
+    true_res = sp.norm(r) / bnorm if bnorm > 0 else 0.0
+    # ---- e2e: the same solve through the host-buffer entry (H2D of b and x0, D2H of x and the defect, every step); the
+    # caller's two vectors are page-locked once (ddm_host_register), as a driver does for its BlockVector storage
+    bw, xw = np.empty_like(b_own), np.empty_like(b_own)
+    ctx.register_host(bw)
+    ctx.register_host(xw)
 
     def solve_e2e():
         np.copyto(bw, b_own)  # b is overwritten by the defect: restore the right-hand side, start from x0 = 0
@@ -335,12 +508,21 @@ def run_b200(a):
         xh, rh = solve_e2e()
     barrier()
     t_e2e = time.perf_counter() - t0
+    ctx.unregister_host(bw)
+    ctx.unregister_host(xw)
     # ---- reduce over ranks
+    its_all = torch.tensor([float(res.iterations), float(res.converged)], dtype=torch.float64)
     vals = torch.tensor([dev_ms, t_wall, t_e2e], dtype=torch.float64)
     if world > 1:
         dist.all_reduce(vals, op=dist.ReduceOp.MAX)
+        lo = its_all.clone()
+        dist.all_reduce(its_all, op=dist.ReduceOp.MAX)
+        dist.all_reduce(lo, op=dist.ReduceOp.MIN)
+        same_its = bool((lo == its_all).all())
+    else:
+        same_its = True
     dev_ms, t_wall, t_e2e = vals.tolist()
-    stats = {k: ctx.stat(k) for k in ("trisolve_fwd", "trisolve_bwd", "trisolve_stored", "spmv", "restrict", "prolong", "coarse", "factor_nnz")}
+    stats = {k: ctx.stat(k) for k in ("trisolve_fwd", "trisolve_bwd", "trisolve_stored", "trisolve_stored_bwd", "spmv", "restrict", "prolong", "coarse", "factor_nnz")}
     per_rank = [None] * world  # load balance of the sharded path: factor entries and sweep times per rank
     fwd_ms, fwd_calls = timers["Schwarz/local solve fwd"]
     bwd_ms, bwd_calls = timers["Schwarz/local solve bwd"]
@@ -353,9 +535,9 @@ def run_b200(a):
         if world > 1:
             dist.barrier()
         return
-    n = P.n
     ms_step = dev_ms / a.steps
-    value = n / (ms_step * 1e-3) / 1e6
+    ok = bool(res.converged) and same_its and true_res <= 1.05 * REDUCTION
+    value = n / (ms_step * 1e-3) / 1e6 if ok else None  # a solve that did not reach 1e-8 has no time-to-1e-8
     peaks = {}
     try:
         peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
@@ -366,41 +548,47 @@ def run_b200(a):
     kern = {}
     for name, ev in (("trisolve_fwd", "Schwarz/local solve fwd"), ("trisolve_bwd", "Schwarz/local solve bwd")):
         ms, calls = timers[ev]
-        kern[name] = {"ms": ms / max(calls, 1), "GBps": stats[name] / (ms / max(calls, 1) * 1e-3) / 1e9 if ms > 0 else None, "launches": calls}
+        kern[name] = {"ms": ms / max(calls, 1), "GBps": stats[name] / (ms / max(calls, 1) * 1e-3) / 1e9 if ms > 0 else None, "launches": calls,
+                      "algorithmic_bytes": stats[name]}
     dom = max(kern, key=lambda k: kern[k]["ms"])
     apply_ms, apply_calls = timers["CombinedPreconditioner/apply"]
     apply_bytes = stats["trisolve_fwd"] + stats["trisolve_bwd"] + stats["restrict"] + stats["prolong"] + stats["coarse"]
-    traffic = None
-    try:
+    traffic = traffic_note = None
+    try:  # ncu dram bytes of the dominant kernel: only a capture of a factor with exactly this many entries counts
         tr = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))
-        traffic = tr.get(f"{'' if a.workload == 'p1cube' else a.workload + '_'}ncell{a.ncell}_nsub{a.nsub}_{a.coarse}_nev{a.nev}_overlap{a.overlap}", {}).get(f"{dom}_kernel")
-    except OSError:
+        for ent in tr.get("captures", []):
+            if int(ent.get("factor_nnz", -1)) == int(stats["factor_nnz"]) and world == 1:
+                traffic, traffic_note = ent.get(f"{dom}_kernel"), ent.get("source")
+    except (OSError, ValueError):
         pass
-    if a.strong and world > 1:
-        traffic = None  # the capture is of one GPU holding all nsub subdomains
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": a.warmup, "ms_per_step": ms_step,
         "higher_is_better": True, "scaling": "strong" if a.strong else "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": workload_name(a, world), "dofs": int(n), "subdomains": int(P.nsub), "coarse_dim": int(P.A0.shape[0]),
-                   "factor_nnz": stats["factor_nnz"], "iterations": int(res.iterations), "converged": bool(res.converged),
-                   "l2_policy": "inputs larger than L2 (factors %.1f GB per sweep vs 126 MB L2)" % (stats["trisolve_stored"] / 1e9)},
+        "config": config_of(a, world, n, nsub, N0),
+        "iterations": int(res.iterations), "converged": bool(res.converged), "factor_nnz": stats["factor_nnz"],
+        "parity": {"true_residual": true_res, "bound": 1.05 * REDUCTION, "iterations_equal_on_all_ranks": same_its, "oracle_iterations": None},
         "time_to_1e-8_s": ms_step * 1e-3, "wall_ms_per_step": t_wall / a.steps * 1e3,
+        "setup_s": {"host": t_setup, "upload_and_device_setup": t_upload},
         "precond_apply": {"ms": apply_ms / max(apply_calls, 1), "algorithmic_GB": apply_bytes / 1e9,
                           "GBps": apply_bytes / (apply_ms / max(apply_calls, 1) * 1e-3) / 1e9 if apply_ms > 0 else None,
                           "frac_of_peak": apply_bytes / (apply_ms / max(apply_calls, 1) * 1e-3) / 1e9 / peak if apply_ms > 0 else None},
-        "e2e": {"value": n / (t_e2e / a.steps) / 1e6, "unit": UNIT, "h2d_bytes_per_step": int(2 * 8 * ctx.n_own), "d2h_bytes_per_step": int(2 * 8 * ctx.n_own)},
+        "e2e": {"value": n / (t_e2e / a.steps) / 1e6 if ok else None, "unit": UNIT, "h2d_bytes_per_step": int(2 * 8 * ctx.n_own), "d2h_bytes_per_step": int(2 * 8 * ctx.n_own)},
         "gpu_launches": int(launches),
         "roofline": {"bound": "hbm", "kernel": f"{dom}_kernel", "achieved": kern[dom]["GBps"], "peak": peak, "unit": "GB/s",
-                     "frac": kern[dom]["GBps"] / peak if kern[dom]["GBps"] else None, "traffic": traffic, "peak_source": peak_src,
-                     "algorithmic_bytes_per_launch": stats[dom], "ms_per_launch": kern[dom]["ms"], "kernels": kern},
+                     "frac": kern[dom]["GBps"] / peak if kern[dom]["GBps"] else None, "traffic": traffic, "traffic_source": traffic_note,
+                     "peak_source": peak_src, "algorithmic_bytes_per_launch": stats[dom], "stored_bytes_per_launch": stats["trisolve_stored" if dom == "trisolve_fwd" else "trisolve_stored_bwd"],
+                     "ms_per_launch": kern[dom]["ms"], "kernels": kern},
         "timers_ms_per_call": {k: (v[0] / max(v[1], 1)) for k, v in timers.items()},
         "clocks": clk.summary(),
         "per_rank": per_rank,
     }
-    if not a.no_cpu_baseline:
-        from oracle import oracle
-
-        line["cpu_baseline"] = cpu_baseline_sample(P, int(res.iterations), a.cpu_seconds, oracle.lib().oracle_max_threads()) if world == 1 else None
+    if not a.no_cpu_baseline and world == 1:
+        t_solve, its_cpu, _, desc, O = cpu_arm(a, world, ctx, L=L, P=P if L is None else None, its_hint=int(res.iterations), budget_s=a.cpu_seconds)
+        if its_cpu is None:
+            t_solve *= int(res.iterations) + 1
+        line["cpu_baseline"] = {"value": n / t_solve / 1e6, "unit": UNIT, "cores": host_cores(), "kind": "port", "sample": desc, "seconds_full_solve_est": t_solve}
+    else:
+        line["cpu_baseline"] = None
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.barrier()

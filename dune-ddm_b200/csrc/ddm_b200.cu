@@ -197,6 +197,17 @@ struct ddm_ctx {
     bool timers_on = false;
     cudaEvent_t sw0 = nullptr, sw1 = nullptr;
     std::vector<TimerRec> trecs;
+    std::vector<cudaEvent_t> ev_pool;  // timer events are recycled: a scope costs two cudaEventRecord, no creation
+    cudaEvent_t take_event()
+    {
+        cudaEvent_t e;
+        if (ev_pool.empty()) cudaEventCreate(&e);
+        else {
+            e = ev_pool.back();
+            ev_pool.pop_back();
+        }
+        return e;
+    }
     std::map<std::string, std::pair<double, int64_t>> tacc;
 };
 
@@ -209,6 +220,10 @@ struct ddm_vec {
     do {                                                          \
         kern<<<(grid), (block), 0, (st)>>>(__VA_ARGS__);          \
         (ctx)->launches++;                                        \
+        {                                                         \
+            cudaError_t le_ = cudaGetLastError();                 \
+            if (le_ != cudaSuccess) return fail("%s:%d launch of %s rejected: %s", __FILE__, __LINE__, #kern, cudaGetErrorString(le_)); \
+        }                                                         \
     } while (0)
 #define LAUNCH(ctx, kern, grid, block, ...) LAUNCH_ON(ctx, (ctx)->s, kern, grid, block, __VA_ARGS__)
 
@@ -227,8 +242,8 @@ struct ScopedTimer {
         if (!c->timers_on) return;
         TimerRec r;
         r.name = name;
-        cudaEventCreate(&r.a);
-        cudaEventCreate(&r.b);
+        r.a = c->take_event();
+        r.b = c->take_event();
         cudaEventRecord(r.a, st);
         c->trecs.push_back(r);
         idx = c->trecs.size() - 1;
@@ -309,6 +324,7 @@ extern "C" int ddm_ctx_destroy(ddm_ctx *c)
         cudaEventDestroy(r.a);
         cudaEventDestroy(r.b);
     }
+    for (auto e : c->ev_pool) cudaEventDestroy(e);
     if (c->comm) g_nccl.CommDestroy(c->comm);
     if (c->blas) cublasDestroy(c->blas);
     if (c->solver) cusolverDnDestroy(c->solver);
@@ -1962,8 +1978,34 @@ extern "C" int ddm_gmres_solve(ddm_ctx *c, ddm_vec *b, ddm_vec *x, double reduct
 // Host vectors are pageable: they pass through the pinned staging area in 2 MB pieces so that the CPU copy of one piece
 // overlaps the DMA of the previous one.
 constexpr int64_t kStageChunk = 1 << 18;
+// A caller that registers its vectors once (ddm_host_register: page-locks them in place) is copied from / to directly.
+static bool host_is_pinned(const void *h)
+{
+    cudaPointerAttributes at;
+    if (cudaPointerGetAttributes(&at, h) != cudaSuccess) {
+        cudaGetLastError();
+        return false;
+    }
+    return at.type == cudaMemoryTypeHost;
+}
+extern "C" int ddm_host_register(ddm_ctx *c, double *h, int64_t count)
+{
+    CU(cudaSetDevice(c->device));
+    CU(cudaHostRegister(h, sizeof(double) * (size_t)count, cudaHostRegisterDefault));
+    return 0;
+}
+extern "C" int ddm_host_unregister(ddm_ctx *c, double *h)
+{
+    CU(cudaSetDevice(c->device));
+    CU(cudaHostUnregister(h));
+    return 0;
+}
 static int stage_in(ddm_ctx *c, ddm_vec *v, const double *h, int slot)
 {
+    if (host_is_pinned(h)) {
+        CU(cudaMemcpyAsync(v->d, h, sizeof(double) * c->n_own, cudaMemcpyHostToDevice, c->s));
+        return 0;
+    }
     double *st = c->h_stage + (int64_t)slot * c->n_own;
     for (int64_t o = 0; o < c->n_own; o += kStageChunk) {
         const int64_t m = std::min(kStageChunk, c->n_own - o);
@@ -1974,6 +2016,11 @@ static int stage_in(ddm_ctx *c, ddm_vec *v, const double *h, int slot)
 }
 static int stage_out(ddm_ctx *c, const ddm_vec *v, double *h, int slot)
 {
+    if (host_is_pinned(h)) {
+        CU(cudaMemcpyAsync(h, v->d, sizeof(double) * c->n_own, cudaMemcpyDeviceToHost, c->s));
+        CU(cudaStreamSynchronize(c->s));
+        return 0;
+    }
     double *st = c->h_stage + (int64_t)slot * c->n_own;
     const int64_t nchunk = (c->n_own + kStageChunk - 1) / kStageChunk;
     while ((int64_t)c->stage_ev.size() < nchunk) {
@@ -2067,8 +2114,8 @@ static void drain_timers(ddm_ctx *c)
         auto &acc = c->tacc[r.name];
         acc.first += ms;
         acc.second += 1;
-        cudaEventDestroy(r.a);
-        cudaEventDestroy(r.b);
+        c->ev_pool.push_back(r.a);
+        c->ev_pool.push_back(r.b);
     }
     c->trecs.clear();
 }

@@ -92,14 +92,33 @@ class Context:
         """Upload the setup products (whole problem, or this rank's shard).  device_galerkin: do not upload P.A0 but
         assemble Z^T A Z on the GPU (ddm_galerkin_assemble); the result is kept in self.A0_device.  with_pou=False uploads no
         partition of unity: restricted Schwarz then applies no weights (schwarz.hh:140, pou == nullptr)."""
-        self = cls(device)
         S = shard(P, rank, world)
+        a, b = S.sub_range
+        N0 = int(P.A0.shape[0])
+        return cls._from_shard(S, [P.pou[i] for i in range(a, b)], [P.factors[i] for i in range(a, b)], [P.Z[i] for i in range(a, b)],
+                               N0, P.A0, device, unique_id, with_coarse, device_galerkin, with_pou, block=P.meta.get("block"))
+
+    @classmethod
+    def from_local(cls, L, device=0, unique_id=None, with_coarse=True, with_pou=True, keep_A0=False):
+        """Upload one rank's own products (setup.local.LocalProducts: nothing global exists on any rank).  L.k_all must hold
+        the coarse-vector counts of all subdomains of the job; the Galerkin matrix is assembled on the devices."""
+        S = L.shard
+        k_all = np.asarray(L.k_all, dtype=np.int64)
+        S.k_offset = int(k_all[: S.sub_range[0]].sum())
+        return cls._from_shard(S, L.pou, L.factors, L.Z, int(k_all.sum()), None, device, unique_id, with_coarse, True, with_pou,
+                               keep_A0=keep_A0)
+
+    @classmethod
+    def _from_shard(cls, S, pou_list, factors, Z_list, N0, A0, device, unique_id, with_coarse, device_galerkin, with_pou, block=None,
+                    keep_A0=True):
+        self = cls(device)
+        rank, world = S.rank, S.world
         self.shard, self.world, self.rank = S, world, rank
         lib = self.lib
         if world > 1:
             uid = (C.c_uint8 * 128)(*unique_id)
             check(lib.ddm_comm_init(self.h, C.c_int(rank), C.c_int(world), uid))
-        if P.meta.get("block") == 3:  # node-major 3x3 blocks: BCRSMatrix<FieldMatrix<double,3,3>>
+        if block == 3:  # node-major 3x3 blocks: BCRSMatrix<FieldMatrix<double,3,3>>
             import scipy.sparse as sp
 
             if S.n_own % 3 or S.n_ghost % 3 or (S.owned[::3] % 3).any() or (S.ghosts[::3] % 3).any():
@@ -116,33 +135,37 @@ class Context:
         if world > 1:
             check(lib.ddm_upload_halo(self.h, C.c_int32(S.peers.size), _p(S.peers, C.c_int32), _p(S.send_ptr, C.c_int64),
                                       _p(S.send_idx, C.c_int32), _p(S.recv_ptr, C.c_int64)))
-        a, b = S.sub_range
-        pou = np.concatenate([P.pou[i] for i in range(a, b)]).astype(np.float64) if b > a else np.zeros(0)
-        check(lib.ddm_upload_decomposition(self.h, C.c_int32(b - a), _p(S.sub_ptr, C.c_int64), _p(S.sub_dofs, C.c_int32),
+        ns = len(factors)
+        pou = np.concatenate(pou_list).astype(np.float64) if ns else np.zeros(0)
+        check(lib.ddm_upload_decomposition(self.h, C.c_int32(ns), _p(S.sub_ptr, C.c_int64), _p(S.sub_dofs, C.c_int32),
                                            _p(pou, C.c_double) if with_pou else None))
-        self.upload_factors(P, a, b)
-        N0 = int(P.A0.shape[0])
+        self._upload_factor_list(factors)
         self.N0 = N0 if with_coarse else 0
         if with_coarse and N0 > 0:
-            k = np.array([P.Z[i].shape[1] for i in range(a, b)], dtype=np.int32)
-            Z = np.concatenate([P.Z[i].ravel(order="F") for i in range(a, b)]) if b > a else np.zeros(1)
-            A0 = np.ascontiguousarray(P.A0, dtype=np.float64)
+            k = np.array([z.shape[1] for z in Z_list], dtype=np.int32)
+            Z = np.concatenate([z.ravel(order="F") for z in Z_list]) if ns else np.zeros(1)
+            if Z.size == 0:
+                Z = np.zeros(1)
+            A0c = None if device_galerkin else np.ascontiguousarray(A0, dtype=np.float64)
             check(lib.ddm_upload_coarse(self.h, _p(k, C.c_int32), _p(np.ascontiguousarray(Z), C.c_double), C.c_int32(N0),
-                                        C.c_int32(S.k_offset), None if device_galerkin else _p(A0, C.c_double)))
+                                        C.c_int32(S.k_offset), None if device_galerkin else _p(A0c, C.c_double)))
         check(lib.ddm_finalize(self.h))
         if with_coarse and N0 > 0 and device_galerkin:
-            self.A0_device = np.empty((N0, N0))
-            check(lib.ddm_galerkin_assemble(self.h, _p(self.A0_device, C.c_double)))
+            self.A0_device = np.empty((N0, N0)) if keep_A0 else None
+            check(lib.ddm_galerkin_assemble(self.h, _p(self.A0_device, C.c_double) if keep_A0 else None))
         return self
 
     def upload_factors(self, P, a, b):
         """ddm_upload_factor / ddm_upload_factor_lu for the hosted subdomains [a, b).  Re-uploading a factor with the same
         symbolic structure only converts the new values in place (device schedules stay valid)."""
+        self._upload_factor_list([P.factors[i] for i in range(a, b)])
+
+    def _upload_factor_list(self, factors):
         lib = self.lib
-        for i in range(a, b):
-            F = P.factors[i]
+        a = 0
+        for i, F in enumerate(factors):
             if hasattr(F, "an"):  # factor.PendingFactor: numeric phase on the device, with the host's symbolic analysis
-                self.factorize(i - a, F)
+                self.factorize(i, F)
                 continue
             if hasattr(F, "xu"):  # non-symmetric subdomain matrix: LU factor (the reference's UMFPack branch, schwarz.hh:85-92)
                 check(lib.ddm_upload_factor_lu(self.h, C.c_int32(i - a), C.c_int32(F.n), C.c_int32(F.nsuper),
@@ -179,6 +202,13 @@ class Context:
     # -- helpers
     def vector(self, values=None):
         return DeviceVector(self, values)
+
+    def register_host(self, arr):
+        """Page-lock a caller's float64 array in place (ddm_host_register): the *_host entries then copy from / to it directly."""
+        check(self.lib.ddm_host_register(self.h, _p(arr, C.c_double), C.c_int64(arr.size)))
+
+    def unregister_host(self, arr):
+        check(self.lib.ddm_host_unregister(self.h, _p(arr, C.c_double)))
 
     def owned(self, global_vec):
         """Restrict a unique-DOF vector to this rank's owned entries."""

@@ -108,7 +108,10 @@ def _sub_job(i):
                 Cm = geneo_gpu.weighted_overlap_matrix(Bn, g["pou"][i])
                 if Cm.nnz == 0 or abs(Cm).max() == 0.0:  # no overlap region: no coarse vector from this subdomain
                     return i, F, np.zeros((s.size, 0), order="F")
-                FK = factor.cholesky_supernodal((An + g["shift"] * Cm).tocsr(), co, g["leaf_size"])
+                K = (An + g["shift"] * Cm).tocsr()
+                K.sort_indices()
+                FK = (factor.PendingFactor(factor.analyse(K, co, g["leaf_size"], symmetric=True), K) if g["numeric"] == "device"
+                      else factor.cholesky_supernodal(K, co, g["leaf_size"]))
                 return i, F, (Cm, FK)
             Zi, ev = coarse_mod.geneo_basis(An, Bn, g["pou"][i], dl, nev=g["nev"], shift=g["shift"], tol=g["eig_tol"],
                                             threshold=g["eig_threshold"], nev_max=g["nev_max"])

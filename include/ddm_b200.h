@@ -200,6 +200,10 @@ int ddm_gmres_solve(ddm_ctx *ctx, ddm_vec *b, ddm_vec *x, double reduction, int3
 
 /* ---- host-pointer forms (stage through pinned memory; owned entries only) ---------------
  * These are what an adaptor with X = Dune::BlockVector<FieldVector<double,1>> calls. */
+/* Optional: page-lock a caller's vector in place (cudaHostRegister) so that the host-pointer entries copy from / to it
+ * directly instead of through the pinned staging area; a driver does this once for its BlockVector storage. */
+int ddm_host_register(ddm_ctx *ctx, double *host, int64_t count);
+int ddm_host_unregister(ddm_ctx *ctx, double *host);
 int ddm_op_apply_host(ddm_ctx *ctx, const double *x, double *y);
 int ddm_op_applyscaleadd_host(ddm_ctx *ctx, double alpha, const double *x, double *y);
 int ddm_dot_host(ddm_ctx *ctx, const double *x, const double *y, double *out);

@@ -64,7 +64,8 @@ sys.path.insert(0, {root!r}); sys.path.insert(0, os.path.join({root!r}, "dune-dd
 import torch.distributed as dist, numpy as np
 import bench
 from ddm_b200 import partition
-sys.argv = ["bench.py", "--ncell", "8", "--nsub", "8", "--gpus", os.environ["WORLD_SIZE"]] + {extra!r}
+sys.argv = ["bench.py", "--ncell", "8", "--nsub", "8", "--gpus", os.environ["WORLD_SIZE"], "--eigensolver", "host", "--numeric", "host",
+            "--setup", "global"] + {extra!r}
 a = bench.parse()
 rank, world, local = bench.dist_env()
 dist.init_process_group("gloo")
@@ -92,7 +93,7 @@ dist.barrier()
 
 
 @pytest.mark.timeout(300)
-@pytest.mark.parametrize("extra", [[], ["--strong"], ["--workload", "q1cube"], ["--workload", "q1cube", "--strong"]],
+@pytest.mark.parametrize("extra", [["--workload", "p1cube"], ["--workload", "p1cube", "--strong"], ["--workload", "q1cube"], ["--workload", "q1cube", "--strong"]],
                          ids=["weak", "strong", "q1-weak", "q1-strong"])
 def test_bench_sharded_setup_under_torchrun(tmp_path, extra):
     """bench.py's N > 1 setup wiring (weak: refined unit cube, 64 -> here 8 subdomains per rank; strong: the N = 1 problem dealt
