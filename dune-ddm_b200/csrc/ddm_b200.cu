@@ -48,6 +48,15 @@ static int fail(const char *fmt, ...)
         ncclResult_t e_ = (call);                                                                        \
         if (e_ != ncclSuccess) return fail("%s:%d %s: %s", __FILE__, __LINE__, #call, g_nccl.GetErrorString(e_)); \
     } while (0)
+// inside ncclGroupStart/End: close the group before leaving on an error
+#define NCG(call)                                                                                        \
+    do {                                                                                                 \
+        ncclResult_t e_ = (call);                                                                        \
+        if (e_ != ncclSuccess) {                                                                         \
+            g_nccl.GroupEnd();                                                                           \
+            return fail("%s:%d %s: %s", __FILE__, __LINE__, #call, g_nccl.GetErrorString(e_));           \
+        }                                                                                                \
+    } while (0)
 #define CK(call)                                                                                         \
     do {                                                                                                 \
         int e_ = (call);                                                                                 \
@@ -191,6 +200,8 @@ struct ddm_ctx {
     std::vector<int32_t> peers;
     std::vector<int64_t> send_ptr, recv_ptr;
     int32_t *send_idx = nullptr;
+    int32_t *rev_tgt = nullptr, *rev_ptr = nullptr, *rev_pos = nullptr;  // reverse halo sum: targets and their buffer positions
+    int64_t rev_ntgt = 0;
     double *sendbuf = nullptr, *recvbuf = nullptr;
     // stats / timers
     std::map<std::string, double> stats;
@@ -262,6 +273,15 @@ static int dev_upload(T **dst, const T *src, size_t count)
     return 0;
 }
 
+struct DevGuard {  // frees the temporaries of a setup routine on every return path
+    std::vector<void *> ptrs;
+    ~DevGuard()
+    {
+        for (void *p : ptrs) cudaFree(p);
+    }
+    void own(const void *p) { ptrs.push_back(const_cast<void *>(p)); }
+};
+
 extern "C" int ddm_ctx_create(int device, ddm_ctx **out)
 {
     int ndev = 0;
@@ -312,7 +332,7 @@ extern "C" int ddm_ctx_destroy(ddm_ctx *c)
     void *ptrs[] = {c->Linv, c->rowptr, c->col, c->val, c->A0, c->A0inv, c->d0, c->y0, c->r0, c->gidx, c->pouP, c->Zp, c->W,
                     c->zoff, c->d_sub_n, c->d_sub_k, c->d_koff, c->seg_ptr, c->segs, c->cpartial, c->dptr, c->dpos,
                     c->fwd_tasks, c->bwd_tasks, c->cnt, c->partial, c->scal, c->send_idx, c->sendbuf,
-                    c->recvbuf};
+                    c->recvbuf, c->rev_tgt, c->rev_ptr, c->rev_pos};
     for (void *p : ptrs) cudaFree(p);
     cudaFreeHost(c->h_scal);
     cudaFreeHost(c->h_stage);
@@ -376,6 +396,29 @@ extern "C" int ddm_upload_halo(ddm_ctx *c, int32_t npeers, const int32_t *peers,
     c->recv_ptr.assign(recv_ptr, recv_ptr + npeers + 1);
     if (c->recv_ptr[npeers] != c->n_ghost) return fail("halo plan covers %lld ghosts, operator has %lld", (long long)c->recv_ptr[npeers], (long long)c->n_ghost);
     CK(dev_upload(&c->send_idx, send_idx, (size_t)c->send_ptr[npeers]));
+    {  // reverse plan: buffer positions grouped by target DOF, ascending position (= ascending peer) inside a group
+        const int64_t ns = c->send_ptr[npeers];
+        if (ns >= INT32_MAX) return fail("halo plan too large");
+        std::vector<int32_t> order(ns);
+        std::iota(order.begin(), order.end(), 0);
+        std::stable_sort(order.begin(), order.end(), [&](int32_t a, int32_t b) { return send_idx[a] < send_idx[b]; });
+        std::vector<int32_t> tgt, ptr;
+        for (int64_t q = 0; q < ns; ++q) {
+            if (q == 0 || send_idx[order[q]] != send_idx[order[q - 1]]) {
+                tgt.push_back(send_idx[order[q]]);
+                ptr.push_back((int32_t)q);
+            }
+        }
+        ptr.push_back((int32_t)ns);
+        c->rev_ntgt = (int64_t)tgt.size();
+        cudaFree(c->rev_tgt);
+        cudaFree(c->rev_ptr);
+        cudaFree(c->rev_pos);
+        c->rev_tgt = c->rev_ptr = c->rev_pos = nullptr;
+        CK(dev_upload(&c->rev_tgt, tgt.data(), tgt.size()));
+        CK(dev_upload(&c->rev_ptr, ptr.data(), ptr.size()));
+        CK(dev_upload(&c->rev_pos, order.data(), order.size()));
+    }
     CU(cudaMalloc((void **)&c->sendbuf, sizeof(double) * std::max<int64_t>(1, c->send_ptr[npeers])));
     CU(cudaMalloc((void **)&c->recvbuf, sizeof(double) * std::max<int64_t>(1, c->send_ptr[npeers])));
     return 0;
@@ -391,10 +434,16 @@ __global__ void pack_kernel(int64_t n, const int32_t *__restrict__ idx, const do
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) buf[i] = v[idx[i]];
 }
-__global__ void unpack_add_kernel(int64_t n, const int32_t *__restrict__ idx, const double *__restrict__ buf, double *__restrict__ v)
+// Reverse halo sum in ONE launch: thread t owns target rev_tgt[t] and adds the received values that belong to it in
+// ascending buffer position, i.e. in ascending peer order (a DOF several peers hold is summed in a fixed order).
+__global__ void unpack_add_kernel(int64_t ntgt, const int32_t *__restrict__ rev_tgt, const int32_t *__restrict__ rev_ptr,
+                                  const int32_t *__restrict__ rev_pos, const double *__restrict__ buf, double *__restrict__ v)
 {
-    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < n) v[idx[i]] += buf[i];
+    const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= ntgt) return;
+    double acc = v[rev_tgt[t]];
+    for (int32_t q = rev_ptr[t]; q < rev_ptr[t + 1]; ++q) acc += buf[rev_pos[q]];
+    v[rev_tgt[t]] = acc;
 }
 
 // owners -> ghosts (copyOwnerToAll, owneroverlapcopy.hh:311-319)
@@ -406,8 +455,8 @@ static int halo_forward(ddm_ctx *c, double *v)
     NC(g_nccl.GroupStart());
     for (int p = 0; p < c->npeers; ++p) {
         const int64_t sc = c->send_ptr[p + 1] - c->send_ptr[p], rc = c->recv_ptr[p + 1] - c->recv_ptr[p];
-        if (sc) NC(g_nccl.Send(c->sendbuf + c->send_ptr[p], sc, ncclDouble, c->peers[p], c->comm, c->s));
-        if (rc) NC(g_nccl.Recv(v + c->n_own + c->recv_ptr[p], rc, ncclDouble, c->peers[p], c->comm, c->s));
+        if (sc) NCG(g_nccl.Send(c->sendbuf + c->send_ptr[p], sc, ncclDouble, c->peers[p], c->comm, c->s));
+        if (rc) NCG(g_nccl.Recv(v + c->n_own + c->recv_ptr[p], rc, ncclDouble, c->peers[p], c->comm, c->s));
     }
     NC(g_nccl.GroupEnd());
     return 0;
@@ -419,14 +468,11 @@ static int halo_reverse_add(ddm_ctx *c, double *v)
     NC(g_nccl.GroupStart());
     for (int p = 0; p < c->npeers; ++p) {
         const int64_t sc = c->send_ptr[p + 1] - c->send_ptr[p], rc = c->recv_ptr[p + 1] - c->recv_ptr[p];
-        if (rc) NC(g_nccl.Send(v + c->n_own + c->recv_ptr[p], rc, ncclDouble, c->peers[p], c->comm, c->s));
-        if (sc) NC(g_nccl.Recv(c->recvbuf + c->send_ptr[p], sc, ncclDouble, c->peers[p], c->comm, c->s));
+        if (rc) NCG(g_nccl.Send(v + c->n_own + c->recv_ptr[p], rc, ncclDouble, c->peers[p], c->comm, c->s));
+        if (sc) NCG(g_nccl.Recv(c->recvbuf + c->send_ptr[p], sc, ncclDouble, c->peers[p], c->comm, c->s));
     }
     NC(g_nccl.GroupEnd());
-    for (int p = 0; p < c->npeers; ++p) { // one launch per peer: duplicates across peers add in peer order
-        const int64_t sc = c->send_ptr[p + 1] - c->send_ptr[p];
-        if (sc) LAUNCH(c, unpack_add_kernel, nblocks(sc), 256, sc, c->send_idx + c->send_ptr[p], c->recvbuf + c->send_ptr[p], v);
-    }
+    if (c->rev_ntgt) LAUNCH(c, unpack_add_kernel, nblocks(c->rev_ntgt), 256, c->rev_ntgt, c->rev_tgt, c->rev_ptr, c->rev_pos, c->recvbuf, v);
     return 0;
 }
 
@@ -560,6 +606,18 @@ static int convert_factor(ddm_ctx *c, int32_t sub, int32_t n, int32_t nsuper, co
         F.rowidx = nullptr;
     }
     if (F.present) free_factor(F);
+    // kept arrays go straight back into F, so that a failure below cannot leak them; until the conversion has succeeded the
+    // factor counts as absent and the context as not finalised (later applies refuse to run on half-converted panels)
+    struct FailGuard {
+        ddm_ctx *c;
+        bool ok = false;
+        ~FailGuard()
+        {
+            if (!ok) c->finalized = false;
+        }
+    } fail_guard{c};
+    F.panel = keep_panel;
+    F.panelU = keep_panelU;
     F.sig = sig;
     F.rowidx = keep_rowidx;
     F.n = n;
@@ -695,11 +753,15 @@ static int convert_factor(ddm_ctx *c, int32_t sub, int32_t n, int32_t nsuper, co
     ConvTile *dconv = nullptr, *dconvU = nullptr;
     SmallInv *dsmall = nullptr;
     int *derr = nullptr;
+    DevGuard tmp_guard;
     CU(cudaMalloc((void **)&daux, sizeof(double) * std::max<int64_t>(1, aux_small + aux_wide)));
+    tmp_guard.own(daux);
     CU(cudaMalloc((void **)&derr, sizeof(int)));
+    tmp_guard.own(derr);
     CU(cudaMemsetAsync(derr, 0, sizeof(int), c->s));
     if (!small.empty()) {
         CK(dev_upload(&dsmall, small.data(), small.size()));
+        tmp_guard.own(dsmall);
         LAUNCH(c, mf_small_inverse_kernel, (int)small.size(), 32, (int32_t)small.size(), dsmall, raw, rawU, daux, lu ? 1 : 0, derr);
     }
     if (!wide.empty()) {
@@ -737,16 +799,16 @@ static int convert_factor(ddm_ctx *c, int32_t sub, int32_t n, int32_t nsuper, co
         }
     }
     CK(dev_upload(&dconv, conv.data(), conv.size()));
-    if (keep_panel) F.panel = keep_panel;
-    else CU(cudaMalloc((void **)&F.panel, sizeof(double) * std::max<int64_t>(1, tile_doubles)));
+    tmp_guard.own(dconv);
+    if (!keep_panel) CU(cudaMalloc((void **)&F.panel, sizeof(double) * std::max<int64_t>(1, tile_doubles)));
     if (!conv.empty()) {
         const int64_t nt = (int64_t)conv.size();
         LAUNCH(c, convert_tiles_kernel, nblocks(nt * 32), 256, nt, dconv, raw, daux, F.panel);
     }
     if (lu) {
         CK(dev_upload(&dconvU, convU.data(), convU.size()));
-        if (keep_panelU) F.panelU = keep_panelU;
-        else CU(cudaMalloc((void **)&F.panelU, sizeof(double) * std::max<int64_t>(1, utile_doubles)));
+        tmp_guard.own(dconvU);
+        if (!keep_panelU) CU(cudaMalloc((void **)&F.panelU, sizeof(double) * std::max<int64_t>(1, utile_doubles)));
         if (!convU.empty()) {
             const int64_t nt = (int64_t)convU.size();
             LAUNCH(c, convert_tiles_kernel, nblocks(nt * 32), 256, nt, dconvU, rawU, daux, F.panelU);
@@ -756,17 +818,12 @@ static int convert_factor(ddm_ctx *c, int32_t sub, int32_t n, int32_t nsuper, co
     CU(cudaMemcpyAsync(&herr, derr, sizeof(int), cudaMemcpyDeviceToHost, c->s));
     CU(cudaStreamSynchronize(c->s));
     CU(cudaGetLastError());
-    cudaFree(daux);
-    cudaFree(dconv);
-    cudaFree(dconvU);
-    cudaFree(dsmall);
-    cudaFree(derr);
     if (herr) {
         c->finalized = false;
         return fail(lu ? "factor of subdomain %d has a zero pivot" : "factor of subdomain %d has a non-positive pivot", sub);
     }
     F.present = true;
-    if (!same) c->finalized = false;
+    fail_guard.ok = same;  // a new structure needs ddm_finalize again
     return 0;
 }
 
@@ -843,14 +900,6 @@ struct ArenaPlan {
         }
         free_[off] = len;
     }
-};
-struct DevGuard {  // frees the temporaries of a setup routine on every return path
-    std::vector<void *> ptrs;
-    ~DevGuard()
-    {
-        for (void *p : ptrs) cudaFree(p);
-    }
-    void own(const void *p) { ptrs.push_back(const_cast<void *>(p)); }
 };
 }  // namespace
 
@@ -1029,9 +1078,12 @@ static int coarse_factor(ddm_ctx *c, const double *A0)
     CU(cudaMemcpyAsync(c->A0inv, c->A0, sizeof(double) * (size_t)N0 * N0, cudaMemcpyDeviceToDevice, c->s));
     // A0^{-1} by dense Cholesky (setup, once; the reference factors A0 with a sparse direct solver on rank 0,
     // galerkin_preconditioner.hh:331-346).
-    cusolverDnHandle_t h;
-    if (cusolverDnCreate(&h) != CUSOLVER_STATUS_SUCCESS) return fail("cusolverDnCreate failed");
-    cusolverDnSetStream(h, c->s);
+    if (!c->solver) {
+        if (cusolverDnCreate(&c->solver) != CUSOLVER_STATUS_SUCCESS) return fail("cusolverDnCreate failed");
+        cusolverDnSetStream(c->solver, c->s);
+    }
+    cusolverDnHandle_t h = c->solver;
+    DevGuard guard;  // work buffers are released on every return path
     // symmetric up to the rounding of its assembly (column blocks are summed in different orders on different ranks)?
     double amax = 0.0, dmax = 0.0;
     for (int i = 0; i < N0; ++i)
@@ -1051,9 +1103,13 @@ static int coarse_factor(ddm_ctx *c, const double *A0)
         double *work = nullptr, *LU = nullptr;
         int *info = nullptr, *ipiv = nullptr;
         CU(cudaMalloc((void **)&work, sizeof(double) * std::max(1, lw)));
+        guard.own(work);
         CU(cudaMalloc((void **)&LU, sizeof(double) * (size_t)N0 * N0));
+        guard.own(LU);
         CU(cudaMalloc((void **)&info, sizeof(int)));
+        guard.own(info);
         CU(cudaMalloc((void **)&ipiv, sizeof(int) * N0));
+        guard.own(ipiv);
         CU(cudaMemcpyAsync(LU, c->A0inv, sizeof(double) * (size_t)N0 * N0, cudaMemcpyDeviceToDevice, c->s));
         cusolverStatus_t st = cusolverDnDgetrf(h, N0, N0, LU, N0, work, ipiv, info);
         CU(cudaMemcpyAsync(&hinfo, info, sizeof(int), cudaMemcpyDeviceToHost, c->s));
@@ -1065,11 +1121,6 @@ static int coarse_factor(ddm_ctx *c, const double *A0)
         CU(cudaMemcpyAsync(&hinfo, info, sizeof(int), cudaMemcpyDeviceToHost, c->s));
         CU(cudaStreamSynchronize(c->s));
         if (st != CUSOLVER_STATUS_SUCCESS || hinfo != 0) return fail("coarse inverse failed (getrs info %d)", hinfo);
-        cudaFree(work);
-        cudaFree(LU);
-        cudaFree(info);
-        cudaFree(ipiv);
-        cusolverDnDestroy(h);
         return 0;
     }
     // Symmetric positive definite: A0 = L L^T, and the apply is  y = L^{-T} (L^{-1} d)  with the explicit triangular inverse:
@@ -1081,14 +1132,13 @@ static int coarse_factor(ddm_ctx *c, const double *A0)
     double *work = nullptr;
     int *info = nullptr;
     CU(cudaMalloc((void **)&work, sizeof(double) * std::max(1, lwork)));
+    guard.own(work);
     CU(cudaMalloc((void **)&info, sizeof(int)));
+    guard.own(info);
     int hinfo = 0;
     cusolverStatus_t st = cusolverDnDpotrf(h, CUBLAS_FILL_MODE_LOWER, N0, c->A0inv, N0, work, lwork, info);
     CU(cudaMemcpyAsync(&hinfo, info, sizeof(int), cudaMemcpyDeviceToHost, c->s));
     CU(cudaStreamSynchronize(c->s));
-    cudaFree(work);
-    cudaFree(info);
-    cusolverDnDestroy(h);
     if (st != CUSOLVER_STATUS_SUCCESS || hinfo != 0) return fail("coarse matrix is not positive definite (potrf info %d)", hinfo);
     if (!c->blas) {
         if (cublasCreate(&c->blas) != CUBLAS_STATUS_SUCCESS) return fail("cublasCreate failed");
@@ -1158,9 +1208,20 @@ extern "C" int ddm_finalize(ddm_ctx *c)
     for (int32_t i = 0; i < c->nsub; ++i)
         if (!c->fac[i].present) return fail("no factor uploaded for subdomain %d", i);
     // release an earlier schedule
+    c->finalized = false;  // a failure below must not leave a half-built schedule marked usable
     void *old[] = {c->gidx, c->pouP, c->Zp, c->W, c->zoff, c->d_sub_n, c->d_sub_k, c->d_koff, c->seg_ptr, c->segs,
                    c->cpartial, c->dptr, c->dpos, c->fwd_tasks, c->bwd_tasks, c->cnt};
     for (void *p : old) cudaFree(p);
+    c->gidx = nullptr;
+    c->pouP = c->Zp = c->W = c->X = c->cpartial = nullptr;
+    c->zoff = nullptr;
+    c->d_sub_n = c->d_sub_k = c->d_koff = c->seg_ptr = c->dptr = c->dpos = nullptr;
+    c->segs = nullptr;
+    c->fwd_tasks = c->bwd_tasks = nullptr;
+    c->cnt = nullptr;
+    cudaFree(c->mf_arena);  // setup scratch of the device factorisation
+    c->mf_arena = nullptr;
+    c->mf_arena_doubles = 0;
 
     const int32_t ns = c->nsub;
     const int64_t P = c->sub_ptr[ns];
@@ -1309,7 +1370,8 @@ extern "C" int ddm_finalize(ddm_ctx *c)
         return a.level != b.level ? a.level < b.level : da < db;
     });
     std::stable_sort(bkeys.begin(), bkeys.end(), [](const Key &a, const Key &b) { return a.level > b.level; });
-    if (const char *e = getenv("DDM_FWD_SKIP")) {  // timing experiments only (results are wrong): drop one class of forward tasks
+#ifdef DDM_TIMING_EXPERIMENTS  // never in the shipped library: dropping a class of forward tasks gives wrong results
+    if (const char *e = getenv("DDM_FWD_SKIP")) {
         const bool drop_diag = strcmp(e, "diag") == 0;
         std::vector<Key> kept;
         for (const Key &k : fkeys)
@@ -1317,6 +1379,7 @@ extern "C" int ddm_finalize(ddm_ctx *c)
         fkeys.swap(kept);
         if (!drop_diag) std::fill(need.begin(), need.end(), 0);
     }
+#endif
     std::vector<TriTask> fwd, bwd;
     fwd.reserve(fkeys.size());
     bwd.reserve(bkeys.size());

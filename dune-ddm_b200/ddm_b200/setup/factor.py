@@ -467,11 +467,30 @@ def lu_supernodal(A, coords=None, leaf_size=32):
 
     The reference factors non-symmetric subdomain matrices with UMFPACK through Dune::UMFPack
     (/root/reference/dune/ddm/schwarz.hh:85-92, extern/dune-istl/dune/istl/umfpack.hh); UMFPACK is absent here, so the
-    factorisation is restated (same unsymmetric-multifrontal family; pivots stay inside a front's diagonal, which is safe
-    for the diffusion-dominated DG matrices this path is used for).
+    factorisation is restated in the same unsymmetric-multifrontal family, but WITHOUT pivoting (UMFPACK pivots with a
+    threshold inside a front): adequate for the diffusion-dominated DG matrices this path is used for, and verified
+    for every factor by check_lu_backward_error, which stops the setup when a solve with the factor is not backward stable.
     """
     A = A.tocsr()
-    return numeric_lu(analyse(A, coords, leaf_size, symmetric=False), A.data)
+    F = numeric_lu(analyse(A, coords, leaf_size, symmetric=False), A.data)
+    check_lu_backward_error(A, F)
+    return F
+
+
+def check_lu_backward_error(A, F, tol=1e-12):
+    """The restated LU does not pivot (UMFPACK, the reference's choice at schwarz.hh:85-92, pivots with a threshold): a tiny
+    pivot would give an inaccurate A_i^{-1} that GPU-vs-oracle parity cannot see, since both consume this factor.  So the
+    factor is probed once at setup: backward error ||A x - d|| / (||A|| ||x|| + ||d||) of a solve with a random right-hand
+    side, in the infinity norm; above `tol` the setup stops."""
+    d = np.random.default_rng(7).standard_normal(A.shape[0])
+    x = solve_supernodal_lu(F, d)
+    if not np.isfinite(x).all():
+        raise np.linalg.LinAlgError("subdomain LU without pivoting broke down (non-finite solution of the probe system)")
+    berr = np.abs(A @ x - d).max() / (abs(A).sum(axis=1).max() * np.abs(x).max() + np.abs(d).max())
+    if berr > tol:
+        raise np.linalg.LinAlgError(f"subdomain LU without pivoting is inaccurate: backward error {berr:.2e} > {tol:.0e} "
+                                    "(the matrix needs the pivoting UMFPACK would do)")
+    return berr
 
 
 def solve_supernodal_lu(F: SupernodalLU, b):

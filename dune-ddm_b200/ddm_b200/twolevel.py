@@ -46,7 +46,10 @@ def _factor_job(i):
         src = np.rint(Ti.data).astype(np.int64) - 1  # A_i.data = A.data[src]
         Ai = sp.csr_matrix((A.data[src], Ti.indices, Ti.indptr), shape=Ti.shape)
         an = factor.analyse(Ai, _G["coords"][s], 32, symmetric=sym)
-        return i, numeric(an, Ai.data), an, src
+        F = numeric(an, Ai.data)
+        if not sym:
+            factor.check_lu_backward_error(Ai, F)  # the restated LU does not pivot: refuse a factor that is not backward stable
+        return i, F, an, src
 
 
 class TwoLevelSchwarzSolver:

@@ -1,6 +1,7 @@
 """Non-symmetric path on the CPU side: the supernodal LU restatement (stand-in for UMFPACK), the oracle's LU
 subdomain solve and LU coarse solve, on config C4's Q1-DG convection-diffusion problem."""
 import numpy as np
+import pytest
 import scipy.sparse.linalg as spla
 
 
@@ -71,3 +72,17 @@ def test_pack_roundtrip_keeps_lu(cd_dg, tmp_path):
     pack.save_products(path, cd_dg)
     Q = pack.load_products(path)
     assert all(np.array_equal(a.xu, b.xu) and np.array_equal(a.x, b.x) for a, b in zip(cd_dg.factors, Q.factors))
+
+
+def test_lu_without_pivoting_refuses_a_matrix_that_needs_it():
+    """the restated LU never pivots; a factor that is not backward stable must stop the setup (UMFPACK would pivot)."""
+    import scipy.sparse as sp
+
+    from ddm_b200.setup import factor
+
+    n = 40
+    A = sp.diags([np.ones(n - 1), np.full(n, 1e-13), 2 * np.ones(n - 1)], [-1, 0, 1]).tocsr()  # tiny pivots, well-conditioned with row swaps
+    with pytest.raises(np.linalg.LinAlgError, match="pivot"):
+        factor.lu_supernodal(A, None, 8)
+    B = sp.diags([-np.ones(n - 1), 4 * np.ones(n), -2 * np.ones(n - 1)], [-1, 0, 1]).tocsr()
+    assert factor.check_lu_backward_error(B, factor.numeric_lu(factor.analyse(B, None, 8, symmetric=False), B.data)) < 1e-14
