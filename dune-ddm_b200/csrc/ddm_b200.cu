@@ -1614,14 +1614,26 @@ static int restrict_all(ddm_ctx *c, const double *d, int with_coarse)
     return 0;
 }
 
+// Coarse residual d0 = Z^T d of all ranks (the reference's gatherv to rank 0, galerkin_preconditioner.hh:171): fixed-order
+// second stage of the fused restriction, then the sum over ranks.  Always on the main stream: the collective stays in the
+// same order as the halo exchanges on every rank.
+static int coarse_gather(ddm_ctx *c)
+{
+    ScopedTimer tm(c, "GalerkinPrec/gather");
+    const int N0 = c->N0;
+    if (c->nranks > 1) CU(cudaMemsetAsync(c->d0, 0, sizeof(double) * N0, c->s));
+    LAUNCH(c, coarse_restrict_final_kernel, c->nsub, 64, c->nsub, c->seg_ptr, c->d_sub_k, c->d_koff, c->cpartial, c->kpad, c->d0);
+    if (c->nranks > 1) NC(g_nccl.AllReduce(c->d0, c->d0, N0, ncclDouble, ncclSum, c->comm, c->s));
+    return 0;
+}
+
+// y0 = A0^{-1} d0, replicated on every GPU (no rank-0 serial solve, no scatter): compute kernels only, so it can run on the
+// side stream beside the cooperative sweeps.
 static int coarse_solve(ddm_ctx *c, cudaStream_t st = nullptr)
 {
     if (!st) st = c->s;
     ScopedTimer tm(c, "GalerkinPrec/coarse solve", st);
     const int N0 = c->N0;
-    if (c->nranks > 1) CU(cudaMemsetAsync(c->d0, 0, sizeof(double) * N0, st));
-    LAUNCH_ON(c, st, coarse_restrict_final_kernel, c->nsub, 64, c->nsub, c->seg_ptr, c->d_sub_k, c->d_koff, c->cpartial, c->kpad, c->d0);
-    if (c->nranks > 1) NC(g_nccl.AllReduce(c->d0, c->d0, N0, ncclDouble, ncclSum, c->comm, st)); // gatherv (galerkin_preconditioner.hh:171)
     const int grid = nblocks((int64_t)N0 * 32);
     if (c->coarse_spd) {  // y = L^{-T} (L^{-1} d0): two triangular GEMVs
         LAUNCH_ON(c, st, dense_gemv_kernel, grid, 256, N0, c->A0inv, c->d0, c->r0, (const double *)nullptr, 1.0, 1);
@@ -1696,6 +1708,7 @@ extern "C" int ddm_coarse_apply(ddm_ctx *c, ddm_vec *d, ddm_vec *x)
     ScopedTimer tm(c, "GalerkinPrec/apply");
     CK(halo_forward(c, d->d));
     CK(restrict_all(c, d->d, 1));
+    CK(coarse_gather(c));
     CK(coarse_solve(c));
     return prolong(c, x->d, 0, 0, 1, 0);
 }
@@ -1717,9 +1730,10 @@ extern "C" int ddm_twolevel_apply(ddm_ctx *c, int type, int mode, int with_coars
         // one restriction and one prolongation serve both levels (the reference does each twice)
         // the coarse solve (a few latency-bound launches) runs on the side stream beside the sweeps
         CK(restrict_all(c, d->d, 1));
-        // (one rank only: with several ranks the coarse all-reduce would sit on SMs the cooperative backward sweep needs and
-        // couple its start to the slowest rank -- measured at 4 GPUs: backward sweep 0.74 -> 1.04 ms)
-        const bool side = c->nranks == 1 && getenv("DDM_NO_SIDE_STREAM") == nullptr;
+        // the sum over ranks stays on the main stream (an NCCL kernel on the side stream sat on SMs the cooperative backward
+        // sweep needed: measured at 4 GPUs, backward sweep 0.74 -> 1.04 ms); what goes to the side stream is compute only
+        CK(coarse_gather(c));
+        const bool side = getenv("DDM_NO_SIDE_STREAM") == nullptr;
         if (side) {
             CU(cudaEventRecord(c->ev_fork, c->s));
             CU(cudaStreamWaitEvent(c->s2, c->ev_fork, 0));
@@ -1740,6 +1754,7 @@ extern "C" int ddm_twolevel_apply(ddm_ctx *c, int type, int mode, int with_coars
     CK(spmv(c, x->d, dn, -1.0, 1));
     CK(halo_forward(c, dn));
     CK(restrict_all(c, dn, 1));
+    CK(coarse_gather(c));
     CK(coarse_solve(c));
     return prolong(c, x->d, 0, 0, 1, 1);
 }

@@ -99,7 +99,8 @@ public:
       check(ddm_upload_operator_bcsr3(c, nb, 0, brp.data(), bci.data(), bva.data()));
     } else
       check(ddm_upload_operator(c, n, 0, p["A_rowptr"].as<std::int64_t>(), p["A_col"].as<std::int32_t>(), p["A_val"].as<double>()));
-    check(ddm_upload_decomposition(c, nsub, p["sub_ptr"].as<std::int64_t>(), p["sub_dofs"].as<std::int32_t>(), p["pou"].as<double>()));
+    check(ddm_upload_decomposition(c, nsub, p["sub_ptr"].as<std::int64_t>(), p["sub_dofs"].as<std::int32_t>(),
+                                   p.has("pou") ? p["pou"].as<double>() : nullptr));  // no partition of unity in the pack: schwarz.hh:140
     const std::int64_t *sp = p["sub_ptr"].as<std::int64_t>();
     for (std::int32_t i = 0; i < nsub; ++i) {
       const std::string f = "F" + std::to_string(i) + "_";

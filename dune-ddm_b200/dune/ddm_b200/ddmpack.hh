@@ -7,6 +7,8 @@
 #include <cstdio>
 #include <cstring>
 #include <map>
+#include <memory>
+#include <type_traits>
 #include <stdexcept>
 #include <string>
 #include <vector>
@@ -23,9 +25,14 @@ struct PackArray {
     for (auto d : dims) c *= d;
     return c;
   }
+  // Typed view; the stored dtype must be the requested one (a foreign or damaged pack must not hand wrongly typed pointers
+  // to the upload calls).
   template <class T>
   const T *as() const
   {
+    const int want = std::is_same<T, double>::value ? 0 : std::is_same<T, std::int32_t>::value ? 1 : std::is_same<T, std::int64_t>::value ? 2
+                     : (std::is_same<T, std::uint8_t>::value || std::is_same<T, unsigned char>::value || std::is_same<T, char>::value) ? 3 : -1;
+    if (want != dtype) throw std::runtime_error("ddmpack: array read with the wrong element type");
     return reinterpret_cast<const T *>(bytes.data());
   }
 };
@@ -34,32 +41,47 @@ class DdmPack {
 public:
   explicit DdmPack(const std::string &path)
   {
-    std::FILE *fh = std::fopen(path.c_str(), "rb");
+    struct Closer {
+      void operator()(std::FILE *f) const { if (f) std::fclose(f); }
+    };
+    std::unique_ptr<std::FILE, Closer> file(std::fopen(path.c_str(), "rb"));  // closed on every path, also when rd() throws
+    std::FILE *fh = file.get();
     if (!fh) throw std::runtime_error("cannot open " + path);
+    std::fseek(fh, 0, SEEK_END);
+    const long long fsize = std::ftell(fh);
+    std::fseek(fh, 0, SEEK_SET);
     char magic[8];
-    if (std::fread(magic, 1, 8, fh) != 8 || std::memcmp(magic, "DDMPACK1", 8) != 0) {
-      std::fclose(fh);
+    if (std::fread(magic, 1, 8, fh) != 8 || std::memcmp(magic, "DDMPACK1", 8) != 0)
       throw std::runtime_error(path + " is not a .ddmpack file");
-    }
     std::int64_t n = 0;
     rd(fh, &n, 8);
+    if (n < 0 || n > (1 << 24)) throw std::runtime_error("ddmpack: implausible array count");
     static const int width[4] = {8, 4, 8, 1};
     for (std::int64_t a = 0; a < n; ++a) {
       std::int32_t ln = 0, code = 0, ndim = 0;
       rd(fh, &ln, 4);
+      if (ln < 0 || ln > 4096) throw std::runtime_error("ddmpack: implausible name length");
       std::string name(ln, '\0');
       rd(fh, name.data(), ln);
       rd(fh, &code, 4);
       rd(fh, &ndim, 4);
+      if (code < 0 || code > 3) throw std::runtime_error("ddmpack: unknown element type in array '" + name + "'");
+      if (ndim < 0 || ndim > 8) throw std::runtime_error("ddmpack: implausible rank of array '" + name + "'");
       PackArray arr;
       arr.dtype = code;
       arr.dims.resize(ndim);
-      rd(fh, arr.dims.data(), 8 * ndim);
-      arr.bytes.resize((std::size_t)arr.count() * width[code]);
+      rd(fh, arr.dims.data(), 8 * (std::size_t)ndim);
+      const long long left = fsize - std::ftell(fh);
+      long long cnt = 1;
+      for (auto d : arr.dims) {
+        if (d < 0 || (d > 0 && cnt > left / d)) throw std::runtime_error("ddmpack: array '" + name + "' is larger than the file");
+        cnt *= d;
+      }
+      if (cnt > left / width[code]) throw std::runtime_error("ddmpack: array '" + name + "' is larger than the file");
+      arr.bytes.resize((std::size_t)cnt * width[code]);
       rd(fh, arr.bytes.data(), arr.bytes.size());
       arrays_.emplace(std::move(name), std::move(arr));
     }
-    std::fclose(fh);
   }
 
   const PackArray &operator[](const std::string &name) const
