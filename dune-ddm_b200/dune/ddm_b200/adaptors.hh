@@ -327,13 +327,16 @@ public:
     Bridge<X>::commit(*ctx_, x, xo);
   }
   Dune::SolverCategory::Category category() const override { return Dune::SolverCategory::nonoverlapping; }
+  const std::shared_ptr<Context> &context() const { return ctx_; }
 
 private:
   std::shared_ptr<Context> ctx_;
 };
 
-/** Fine level first, coarse level second (the order of examples/poisson.cc:305-306); both levels then run as
- *  one fused pass on the GPU (ddm_twolevel_apply). */
+/** Any list of preconditioners, applied in the order they were added (combined_preconditioner.hh:90-109,127-163).
+ *  The reference's own pair -- Schwarz level first, Galerkin level second (examples/poisson.cc:305-306) -- on one
+ *  context runs as one fused pass on the GPU (ddm_twolevel_apply); every other list (a third level, the coarse level
+ *  first, a foreign Dune::Preconditioner) is applied level by level exactly as the reference does. */
 template <class X>
 class CombinedPreconditioner : public Dune::Preconditioner<X, X> {
 public:
@@ -344,31 +347,69 @@ public:
     else DUNE_THROW(Dune::NotImplemented, "Unknown apply mode '" << mode << "'"); // combined_preconditioner.hh:66
   }
   void set_op(std::shared_ptr<Dune::LinearOperator<X, X>> op) { op_ = std::move(op); } // :111
-  void add(std::shared_ptr<SchwarzPreconditioner<X>> fine) { fine_ = std::move(fine); }
-  void add(std::shared_ptr<GalerkinPreconditioner<X>> coarse)
+  void add(std::shared_ptr<Dune::Preconditioner<X, X>> prec)
   {
-    if (!fine_) DUNE_THROW(Dune::Exception, "add the Schwarz level before the Galerkin level");
-    coarse_ = std::move(coarse);
+    if (!precs_.empty() && prec->category() != precs_[0]->category())
+      DUNE_THROW(Dune::Exception, "ERROR: Categories of the new preconditioner does not match"); // :92-96
+    precs_.push_back(std::move(prec));
+    fine_ = precs_.size() <= 2 ? std::dynamic_pointer_cast<SchwarzPreconditioner<X>>(precs_[0]) : nullptr;
+    coarse_ = precs_.size() == 2 ? std::dynamic_pointer_cast<GalerkinPreconditioner<X>>(precs_[1]) : nullptr;
+    fused_ = fine_ && (precs_.size() == 1 || (coarse_ && coarse_->context() == fine_->context()));
   }
-  void pre(X &, X &) override {}
-  void post(X &) override {}
+  void pre(X &x, X &b) override
+  {
+    for (auto &p : precs_) p->pre(x, b);
+  }
+  void post(X &x) override
+  {
+    for (auto &p : precs_) p->post(x);
+  }
   void apply(X &x, const X &d) override
   {
-    if (!fine_) DUNE_THROW(Dune::Exception, "No preconditioners added");
-    if (mode_ == ApplyMode::Multiplicative && coarse_ && !op_)
-      DUNE_THROW(Dune::Exception, "Multiplicative mode needs the operator, call set_op"); // :147
-    Context &c = *fine_->context();
-    ddm_vec *di = Bridge<X>::in(c, d, 0), *xo = Bridge<X>::out(c, x, 1);
-    check(ddm_twolevel_apply(c.handle(), (int)fine_->type(), (int)mode_, coarse_ ? 1 : 0, di, xo));
-    Bridge<X>::commit(c, x, xo);
+    if (precs_.empty()) DUNE_THROW(Dune::Exception, "No preconditioners added");
+    if (mode_ == ApplyMode::Multiplicative && precs_.size() > 1 && !op_)
+      DUNE_THROW(Dune::Exception, "ERROR: ApplyMode is multiplicative but operator A is not provided. Set with `set_op`"); // :147
+    if (fused_) {
+      Context &c = *fine_->context();
+      ddm_vec *di = Bridge<X>::in(c, d, 0), *xo = Bridge<X>::out(c, x, 1);
+      check(ddm_twolevel_apply(c.handle(), (int)fine_->type(), (int)mode_, coarse_ ? 1 : 0, di, xo));
+      Bridge<X>::commit(c, x, xo);
+      return;
+    }
+    // generic list: combined_preconditioner.hh:132-158, level by level
+    x = 0;
+    precs_[0]->apply(x, d);
+    X xnext(x);
+    if (mode_ == ApplyMode::Additive) {
+      for (std::size_t i = 1; i < precs_.size(); ++i) {
+        xnext = 0;
+        precs_[i]->apply(xnext, d);
+        x += xnext;
+      }
+    }
+    else {
+      X dnext(d);
+      for (std::size_t i = 1; i < precs_.size(); ++i) {
+        op_->applyscaleadd(-1.0, x, dnext);
+        xnext = 0;
+        precs_[i]->apply(xnext, dnext);
+        x += xnext;
+      }
+    }
   }
-  Dune::SolverCategory::Category category() const override { return Dune::SolverCategory::nonoverlapping; }
+  Dune::SolverCategory::Category category() const override
+  {
+    return precs_.empty() ? Dune::SolverCategory::nonoverlapping : precs_[0]->category();
+  }
+  bool fused() const { return fused_; }
 
 private:
   ApplyMode mode_ = ApplyMode::Additive;
   std::shared_ptr<Dune::LinearOperator<X, X>> op_;
+  std::vector<std::shared_ptr<Dune::Preconditioner<X, X>>> precs_;
   std::shared_ptr<SchwarzPreconditioner<X>> fine_;
   std::shared_ptr<GalerkinPreconditioner<X>> coarse_;
+  bool fused_ = false;
 };
 
 } // namespace Dune::ddm_b200

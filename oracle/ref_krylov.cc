@@ -237,6 +237,23 @@ int main(int argc, char **argv)
       res = run<DeviceVector>(solver, op, sp, prec, reduction, maxit, restart, x, bd);
       hist = sp->norms;
       x.download(xh);
+    } else if (arm == "gpu-list") {
+      // a list the fused pass does not cover -- the coarse level added first, then the Schwarz level: applied level by
+      // level as combined_preconditioner.hh:132-158 does (the generic branch of the drop-in CombinedPreconditioner)
+      auto ctx = Context::fromPack(pack, 0, with_coarse);
+      DeviceVector x(ctx), bd(ctx);
+      x.upload(xh);
+      bd.upload(bh);
+      auto op = std::make_shared<NonOverlappingOperator<DeviceVector>>(ctx);
+      auto sp = std::make_shared<RecordingScalarProduct<DeviceVector>>(std::make_shared<NonOverlappingScalarProduct<DeviceVector>>(ctx));
+      auto prec = std::make_shared<CombinedPreconditioner<DeviceVector>>(mode);
+      prec->set_op(op);
+      if (with_coarse) prec->add(std::make_shared<GalerkinPreconditioner<DeviceVector>>(ctx));
+      prec->add(std::make_shared<SchwarzPreconditioner<DeviceVector>>(ctx, stype));
+      if (with_coarse && prec->fused()) DUNE_THROW(Dune::Exception, "the reversed list must not take the fused pass");
+      res = run<DeviceVector>(solver, op, sp, prec, reduction, maxit, restart, x, bd);
+      hist = sp->norms;
+      x.download(xh);
     } else
       DUNE_THROW(Dune::Exception, "unknown arm " << arm);
     const double wall = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();

@@ -80,6 +80,22 @@ def test_dune_cgsolver_drives_the_gpu_path(packed, tmp_path, arm):
 
 @needs_bin
 @pytest.mark.gpu
+def test_generic_preconditioner_list_goes_level_by_level(packed, tmp_path):
+    """CombinedPreconditioner::add takes any list (combined_preconditioner.hh:90-109): with the coarse level added first
+    the drop-in class cannot use its fused pass and applies the levels one by one as the reference does (:132-158).  The
+    additive sum commutes, so Dune::CGSolver must behave as with the usual order."""
+    P, path = packed
+    rc, xc = run("cpu", path, "cg", str(tmp_path / "xc.bin"))
+    rg, xg = run("gpu-list", path, "cg", str(tmp_path / "xg.bin"))
+    assert rg["converged"] and abs(rg["iterations"] - rc["iterations"]) <= 1
+    assert np.linalg.norm(xg - xc) <= 1e-8 * np.linalg.norm(xc)
+    # multiplicative with the coarse level first is a different (non-symmetric) method: it must run and converge under GMRES
+    rm, xm = run("gpu-list", path, "gmres", str(tmp_path / "xm.bin"), typ="restricted", mode="multiplicative")
+    assert rm["converged"] and np.linalg.norm(P.b - P.A @ xm) <= 1e-5 * np.linalg.norm(P.b)
+
+
+@needs_bin
+@pytest.mark.gpu
 @pytest.mark.parametrize("arm", ["gpu", "gpu-host"])
 def test_dune_gmres_drives_the_gpu_path(packed, tmp_path, arm):
     P, path = packed

@@ -20,7 +20,9 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 # (sub-solve vs oracle, backward error, schwarz, coarse, two-level); None = not applicable
 BOUNDS = {
-    "C2": dict(solve=1e-12, berr=1e-14, schwarz=1e-12, coarse=1e-12, twolevel=1e-12),
+    # coarse / two-level: cond(A0) = 4.4e8, two FP64 solves of the Galerkin system differ by up to cond(A0) eps = 5e-8 (see
+    # coarse_gpu_vs_refined / coarse_oracle_vs_refined in the report: both sit at the same distance from the refined solve)
+    "C2": dict(solve=1e-12, berr=1e-14, schwarz=1e-12, coarse=3e-8, twolevel=2e-8),
     "C3": dict(solve=1e-12, berr=1e-14, schwarz=1e-12, coarse=1e-12, twolevel=1e-12),
     "C4": dict(solve=1e-12, berr=1e-14, schwarz=1e-12, coarse=1e-12, twolevel=1e-12),
     "C5brick": dict(solve=1e-12, berr=1e-14, schwarz=1e-12, coarse=1e-12, twolevel=1e-12),
@@ -56,6 +58,25 @@ def blockdiag(P):
                       subs=[np.arange(off[i], off[i + 1], dtype=np.int64) for i in range(P.nsub)], pou=[np.ones(int(k)) for k in sizes],
                       factors=P.factors, Z=[np.zeros((int(k), 0), order="F") for k in sizes], A0=np.zeros((0, 0)), n_novlp=sizes.copy(), meta=dict(kind="blockdiag"))
     return Q, Ais, off
+
+
+def coarse_reference(P, d):
+    """x = sum_i R_i^T Z_i y_i with A0 y = (Z_i^T R_i d)_i solved to working accuracy: LU solve plus iterative refinement with
+    the residual in long double (galerkin_preconditioner.hh:151-194 in exact arithmetic, for all practical purposes)."""
+    import scipy.linalg as sla
+
+    off = np.concatenate(([0], np.cumsum([z.shape[1] for z in P.Z])))
+    d0 = np.concatenate([z.T @ d[s] for z, s in zip(P.Z, P.subs)])
+    lu = sla.lu_factor(P.A0)
+    y = sla.lu_solve(lu, d0)
+    A0l, d0l = P.A0.astype(np.longdouble), d0.astype(np.longdouble)
+    for _ in range(4):
+        r = (d0l - A0l @ y.astype(np.longdouble)).astype(np.float64)
+        y = y + sla.lu_solve(lu, r)
+    x = np.zeros(P.n)
+    for i, (z, s) in enumerate(zip(P.Z, P.subs)):
+        np.add.at(x, s, z @ y[off[i] : off[i + 1]])
+    return x
 
 
 def inf(v):
@@ -115,7 +136,13 @@ def test_parity_numbers_at_config_size(name):
     rep["schwarz_max"] = per_sub(xvec.download(), O.schwarz_apply(dg, restricted=kw["restricted"]))
     dvec.upload(dg)
     G.apply(xvec, dvec)
-    rep["coarse_max"] = per_sub(xvec.download(), O.coarse_apply(dg))
+    xc_gpu, xc_orc = xvec.download(), O.coarse_apply(dg)
+    rep["coarse_max"] = per_sub(xc_gpu, xc_orc)
+    # Two FP64 solves of A0 y = d0 by different factorisations differ by up to cond(A0) eps in the forward error, whatever
+    # their quality: measure both against the coarse correction computed with a refined solve (residuals in extended precision)
+    xc_ref = coarse_reference(P, dg)
+    rep["coarse_gpu_vs_refined"] = per_sub(xc_gpu, xc_ref)
+    rep["coarse_oracle_vs_refined"] = per_sub(xc_orc, xc_ref)
     op = api.NonOverlappingOperator(ctx)
     Cp = api.CombinedPreconditioner(kw["mode"])
     Cp.set_op(op)
