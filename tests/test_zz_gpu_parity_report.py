@@ -20,12 +20,16 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 # (sub-solve vs oracle, backward error, schwarz, coarse, two-level); None = not applicable
 BOUNDS = {
-    # coarse / two-level: cond(A0) = 4.4e8, two FP64 solves of the Galerkin system differ by up to cond(A0) eps = 5e-8 (see
-    # coarse_gpu_vs_refined / coarse_oracle_vs_refined in the report: both sit at the same distance from the refined solve)
-    "C2": dict(solve=1e-12, berr=1e-14, schwarz=1e-12, coarse=3e-8, twolevel=2e-8),
-    "C3": dict(solve=1e-12, berr=1e-14, schwarz=1e-12, coarse=1e-12, twolevel=1e-12),
-    "C4": dict(solve=1e-12, berr=1e-14, schwarz=1e-12, coarse=1e-12, twolevel=1e-12),
-    "C5brick": dict(solve=1e-12, berr=1e-14, schwarz=1e-12, coarse=1e-12, twolevel=1e-12),
+    # Subdomain solves, their backward errors and the Schwarz level hold north_star's 1e-12 everywhere (measured <= 3e-15).
+    # Coarse and two-level applications are limited by the Galerkin solve: two FP64 solves of A0 y = d0 by different
+    # factorisations (cuSOLVER potrf + explicit L^{-1} on the device, LAPACK potrf + substitution in the oracle) differ by up
+    # to cond(A0) eps in the forward error whatever their quality -- the report's coarse_gpu_vs_refined and
+    # coarse_oracle_vs_refined (both against a solve refined in extended precision) sit at the same distance.  Bounds below
+    # are ten times the values measured on a B200 (profiles/r02_parity_report.json), cond(A0) beside them:
+    "C2": dict(solve=1e-12, berr=1e-14, schwarz=1e-12, coarse=3e-8, twolevel=2e-8),  # cond(A0) 4.4e8: measured 2.7e-9 / 1.1e-9
+    "C3": dict(solve=1e-12, berr=1e-14, schwarz=1e-12, coarse=7e-11, twolevel=7e-11),  # cond(A0) 9.2e6: measured 6.6e-12 / 6.4e-12
+    "C4": dict(solve=1e-12, berr=1e-14, schwarz=1e-12, coarse=1.5e-10, twolevel=8e-10),  # cond(A0) 7.7e8: measured 1.5e-11 / 7.6e-11
+    "C5brick": dict(solve=1e-12, berr=1e-14, schwarz=1e-12, coarse=1e-12, twolevel=1e-12),  # cond(A0) 6.9e6: measured 2.2e-14 / 3.5e-15
 }
 
 
@@ -163,4 +167,6 @@ def test_parity_numbers_at_config_size(name):
     assert rep["solve_vs_oracle_max"] <= B["solve"], rep
     assert rep["schwarz_max"] <= B["schwarz"], rep
     assert rep["coarse_max"] <= B["coarse"], rep
+    # the device's coarse solve is as accurate as the oracle's (distance to the refined solve within a factor of ten)
+    assert rep["coarse_gpu_vs_refined"] <= 10 * max(rep["coarse_oracle_vs_refined"], 1e-13), rep
     assert rep["twolevel_max"] <= B["twolevel"], rep
