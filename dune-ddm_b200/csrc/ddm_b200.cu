@@ -7,6 +7,7 @@
 
 #include <cooperative_groups.h>
 #include <cuda_runtime.h>
+#include <cuda_profiler_api.h>
 #include <cublas_v2.h>
 #include <cusolverDn.h>
 #include <dlfcn.h>
@@ -2236,6 +2237,14 @@ extern "C" int ddm_stopwatch_stop(ddm_ctx *c, double *ms)
     return 0;
 }
 extern "C" int64_t ddm_kernel_launches(ddm_ctx *c) { return c->launches; }
+// Profiler range (cudaProfilerStart / Stop) so that `ncu --profile-from-start off` sees the solve phase only, not the setup.
+extern "C" int ddm_profiler_range(ddm_ctx *c, int on)
+{
+    CU(cudaStreamSynchronize(c->s));
+    if (on) CU(cudaProfilerStart());
+    else CU(cudaProfilerStop());
+    return 0;
+}
 extern "C" int ddm_sync(ddm_ctx *c)
 {
     CU(cudaStreamSynchronize(c->s));

@@ -17,7 +17,7 @@ SYMBOLS = [
     "ddm_op_apply", "ddm_op_applyscaleadd", "ddm_dot", "ddm_norm", "ddm_schwarz_apply", "ddm_coarse_apply",
     "ddm_twolevel_apply", "ddm_pcg_solve", "ddm_gmres_solve", "ddm_gmres_solve_host", "ddm_op_apply_host", "ddm_op_applyscaleadd_host", "ddm_dot_host",
     "ddm_twolevel_apply_host", "ddm_pcg_solve_host", "ddm_host_register", "ddm_host_unregister", "ddm_get_stat", "ddm_timers_enable", "ddm_timers_reset",
-    "ddm_get_timer", "ddm_stopwatch_start", "ddm_stopwatch_stop", "ddm_kernel_launches", "ddm_sync",
+    "ddm_get_timer", "ddm_stopwatch_start", "ddm_stopwatch_stop", "ddm_kernel_launches", "ddm_profiler_range", "ddm_sync",
 ]
 
 

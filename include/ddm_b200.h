@@ -228,6 +228,8 @@ int ddm_get_timer(ddm_ctx *ctx, const char *event, double *total_ms, int64_t *ca
 int ddm_stopwatch_start(ddm_ctx *ctx);
 int ddm_stopwatch_stop(ddm_ctx *ctx, double *elapsed_ms);
 int64_t ddm_kernel_launches(ddm_ctx *ctx);
+/* cudaProfilerStart / cudaProfilerStop around a region of interest (ncu --profile-from-start off). */
+int ddm_profiler_range(ddm_ctx *ctx, int on);
 int ddm_sync(ddm_ctx *ctx);
 
 #ifdef __cplusplus
