@@ -146,6 +146,11 @@ struct ddm_ctx {
     int32_t *rowptr = nullptr, *col = nullptr;
     double *val = nullptr;
     int spmv_group = 8;
+    int64_t *sell_ptr = nullptr;  // sliced-ELL copy of the scalar operator (build_sell); null: CSR kernel
+    int32_t *sell_col = nullptr;
+    double *sell_val = nullptr;
+    int64_t sell_entries = 0;
+    std::vector<int64_t> sell_pos;  // CSR entry -> position in sell_val (value updates)
     int block = 1;       // 1: scalar CSR, 3: 3x3 block CSR (rowptr/col index blocks, val holds 9 doubles per block)
     int64_t nb_own = 0;  // block rows
     // decomposition
@@ -333,7 +338,7 @@ extern "C" int ddm_ctx_destroy(ddm_ctx *c)
     void *ptrs[] = {c->Linv, c->rowptr, c->col, c->val, c->A0, c->A0inv, c->d0, c->y0, c->r0, c->gidx, c->pouP, c->Zp, c->W,
                     c->zoff, c->d_sub_n, c->d_sub_k, c->d_koff, c->seg_ptr, c->segs, c->cpartial, c->dptr, c->dpos,
                     c->fwd_tasks, c->bwd_tasks, c->cnt, c->partial, c->scal, c->send_idx, c->sendbuf,
-                    c->recvbuf, c->rev_tgt, c->rev_ptr, c->rev_pos};
+                    c->recvbuf, c->rev_tgt, c->rev_ptr, c->rev_pos, c->sell_ptr, c->sell_col, c->sell_val};
     for (void *p : ptrs) cudaFree(p);
     cudaFreeHost(c->h_scal);
     cudaFreeHost(c->h_stage);
@@ -478,6 +483,54 @@ static int halo_reverse_add(ddm_ctx *c, double *v)
 }
 
 // ------------------------------------------------------------------------------------------------ uploads
+// Sliced-ELL copy of the scalar operator for spmv_sell_kernel (kernels.cuh), kept when padding every slice of 32 rows to its
+// longest row costs less than 10 % of the entries; otherwise the CSR kernel stays in charge.
+static int build_sell(ddm_ctx *c, const int32_t *rp, const int32_t *col, const double *val)
+{
+    cudaFree(c->sell_ptr);
+    cudaFree(c->sell_col);
+    cudaFree(c->sell_val);
+    c->sell_ptr = nullptr;
+    c->sell_col = nullptr;
+    c->sell_val = nullptr;
+    c->sell_pos.clear();
+    if (getenv("DDM_NO_SELL") || c->n_own == 0) return 0;
+    const int64_t n = c->n_own, nslice = (n + 31) / 32;
+    std::vector<int64_t> ptr(nslice + 1, 0);
+    for (int64_t s = 0; s < nslice; ++s) {
+        int32_t w = 0;
+        for (int64_t r = s * 32; r < std::min(n, s * 32 + 32); ++r) w = std::max(w, rp[r + 1] - rp[r]);
+        ptr[s + 1] = ptr[s] + (int64_t)w * 32;
+    }
+    const int64_t tot = ptr[nslice];
+    if ((double)tot > 1.10 * (double)c->nnz + 1024.0) return 0;
+    std::vector<int32_t> scol(tot);
+    std::vector<double> sval(tot, 0.0);
+    c->sell_pos.resize(c->nnz);
+    for (int64_t s = 0; s < nslice; ++s) {
+        const int32_t w = (int32_t)((ptr[s + 1] - ptr[s]) / 32);
+        for (int l = 0; l < 32; ++l) {
+            const int64_t r = s * 32 + l;
+            const int32_t own = (int32_t)std::min<int64_t>(r, n - 1);
+            const int32_t len = r < n ? rp[r + 1] - rp[r] : 0;
+            for (int32_t k = 0; k < w; ++k) {
+                const int64_t o = ptr[s] + (int64_t)k * 32 + l;
+                if (k < len) {
+                    scol[o] = col[rp[r] + k];
+                    sval[o] = val[rp[r] + k];
+                    c->sell_pos[rp[r] + k] = o;
+                } else
+                    scol[o] = own;  // padding: value 0 times the row's own entry
+            }
+        }
+    }
+    CK(dev_upload(&c->sell_ptr, ptr.data(), ptr.size()));
+    CK(dev_upload(&c->sell_col, scol.data(), scol.size()));
+    CK(dev_upload(&c->sell_val, sval.data(), sval.size()));
+    c->sell_entries = tot;
+    return 0;
+}
+
 extern "C" int ddm_upload_operator(ddm_ctx *c, int64_t n_own, int64_t n_ghost, const int64_t *rowptr, const int32_t *col,
                                    const double *val)
 {
@@ -495,6 +548,7 @@ extern "C" int ddm_upload_operator(ddm_ctx *c, int64_t n_own, int64_t n_ghost, c
     CK(dev_upload(&c->rowptr, rp.data(), rp.size()));
     CK(dev_upload(&c->col, col, (size_t)nnz));
     CK(dev_upload(&c->val, val, (size_t)nnz));
+    CK(build_sell(c, rp.data(), col, val));
     const double mean = n_own ? (double)nnz / (double)n_own : 1.0;
     // lanes per row: measured on B200 at 15 nnz/row (3-D P1): G=4 60 us, G=8 91 us, G=16 149 us for 21.6 M nonzeros --
     // short dependent chains per lane beat idle lanes, so a lane takes about four entries of its row
@@ -542,6 +596,11 @@ extern "C" int ddm_update_operator_values(ddm_ctx *c, const double *val)
     if (!c->rowptr) return fail("no operator uploaded");
     CU(cudaMemcpyAsync(c->val, val, sizeof(double) * (size_t)c->nnz, cudaMemcpyHostToDevice, c->s));
     CU(cudaStreamSynchronize(c->s));
+    if (c->sell_ptr) {  // refresh the sliced-ELL copy (padding stays zero)
+        std::vector<double> sval((size_t)c->sell_entries, 0.0);
+        for (int64_t k = 0; k < c->nnz; ++k) sval[c->sell_pos[k]] = val[k];
+        CU(cudaMemcpy(c->sell_val, sval.data(), sizeof(double) * sval.size(), cudaMemcpyHostToDevice));
+    }
     return 0;
 }
 
@@ -1557,6 +1616,10 @@ static int spmv(ddm_ctx *c, double *x, double *y, double alpha, int mode)
         case 16: LAUNCH(c, spmv_bcsr3_kernel<16>, gridb, 256, c->nb_own, c->rowptr, c->col, c->val, x, y, alpha, mode); break;
         default: LAUNCH(c, spmv_bcsr3_kernel<32>, gridb, 256, c->nb_own, c->rowptr, c->col, c->val, x, y, alpha, mode); break;
         }
+        return 0;
+    }
+    if (c->sell_ptr) {
+        LAUNCH(c, spmv_sell_kernel, nblocks(((c->n_own + 31) / 32) * 32), 256, c->n_own, c->sell_ptr, c->sell_col, c->sell_val, x, y, alpha, mode);
         return 0;
     }
     const int grid = nblocks(c->n_own * G);

@@ -39,6 +39,42 @@ __global__ void __launch_bounds__(256) spmv_csr_kernel(int64_t n, const int32_t 
     }
 }
 
+// K1s  the same product from a sliced-ELL copy of the matrix (slices of 32 rows, entries of a slice stored column by column:
+// entry k of row r sits at ptr[slice] + k*32 + lane).  One thread per row: every load of the value / column streams is one
+// contiguous 256 / 128 byte segment per warp, all loads of a row are independent (no row-pointer indirection, no cross-lane
+// reduction), and the row sum runs in ascending column order -- the order of BCRSMatrix::mv (bcrsmatrix.hh:1652-1660).  Used
+// when padding the slices to their longest row costs < 10 % (structured and quasi-uniform meshes); padded entries carry
+// value 0 and the row's own column.
+__global__ void __launch_bounds__(256) spmv_sell_kernel(int64_t n, const int64_t *__restrict__ ptr, const int32_t *__restrict__ col,
+                                                        const double *__restrict__ val, const double *__restrict__ x,
+                                                        double *__restrict__ y, double alpha, int mode)
+{
+    const int64_t row = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t slice = row >> 5;
+    if (slice * 32 >= n) return;
+    const int64_t b = ptr[slice] + (threadIdx.x & 31);
+    const int w = (int)((ptr[slice + 1] - ptr[slice]) >> 5);
+    double acc = 0.0;
+    int k = 0;
+    for (; k + 4 <= w; k += 4) {
+        const int64_t o = b + (int64_t)k * 32;
+        const int32_t c0 = __ldcs(col + o), c1 = __ldcs(col + o + 32), c2 = __ldcs(col + o + 64), c3 = __ldcs(col + o + 96);
+        const double v0 = __ldcs(val + o), v1 = __ldcs(val + o + 32), v2 = __ldcs(val + o + 64), v3 = __ldcs(val + o + 96);
+        acc = fma(v0, __ldg(x + c0), acc);
+        acc = fma(v1, __ldg(x + c1), acc);
+        acc = fma(v2, __ldg(x + c2), acc);
+        acc = fma(v3, __ldg(x + c3), acc);
+    }
+    for (; k < w; ++k) {
+        const int64_t o = b + (int64_t)k * 32;
+        acc = fma(__ldcs(val + o), __ldg(x + __ldcs(col + o)), acc);
+    }
+    if (row < n) {
+        if (mode == 0) y[row] = acc;
+        else y[row] += alpha * acc;
+    }
+}
+
 // K1b  block-CSR SpMV with 3x3 blocks (BCRSMatrix<FieldMatrix<double,3,3>>, linear elasticity): same entry points as K1.
 // The 9*nblk values of a block row are one contiguous stream; G lanes walk it element by element (fully coalesced: lane t
 // reads value e = 9*first + t, t + G, ...), element e belongs to block e/9, row (e%9)/3, column e%3 of that block.  Each
@@ -216,18 +252,19 @@ struct Segment {
     int32_t local0;   // start - base of the subdomain
 };
 
-__global__ void __launch_bounds__(256) restrict_kernel(const Segment *__restrict__ segs, const int32_t *__restrict__ gidx,
-                                                       const double *__restrict__ d, double *__restrict__ W,
-                                                       double *__restrict__ W2, int with_coarse,
-                                                       const int64_t *__restrict__ zoff, const int32_t *__restrict__ sub_n,
-                                                       const int32_t *__restrict__ sub_k, const double *__restrict__ Zp,
-                                                       double *__restrict__ partial /* [nseg][kpad] */, int kpad)
+__global__ void __launch_bounds__(256, 3) restrict_kernel(const Segment *__restrict__ segs, const int32_t *__restrict__ gidx,
+                                                          const double *__restrict__ d, double *__restrict__ W,
+                                                          double *__restrict__ W2, int with_coarse,
+                                                          const int64_t *__restrict__ zoff, const int32_t *__restrict__ sub_n,
+                                                          const int32_t *__restrict__ sub_k, const double *__restrict__ Zp,
+                                                          double *__restrict__ partial /* [nseg][kpad] */, int kpad)
 {
-    __shared__ double sm[8];
+    __shared__ double sm[8][kKmax];
     const Segment sg = segs[blockIdx.x];
     const int k = with_coarse ? sub_k[sg.sub] : 0;
     const int32_t ni = sub_n[sg.sub];
     const double *Zi = with_coarse ? Zp + zoff[sg.sub] + sg.local0 : nullptr;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     for (int k0 = 0; k0 < (k > 0 ? k : 1); k0 += kKmax) {
         double acc[kKmax];
 #pragma unroll
@@ -239,22 +276,35 @@ __global__ void __launch_bounds__(256) restrict_kernel(const Segment *__restrict
                 W[p] = v;
                 if (W2) W2[p] = 0.0;
             }
-            // all basis loads of this position are issued before the first use (the compiler otherwise pairs each load
-            // with its FMA and keeps two in flight)
-            double z[kKmax];
+            // the basis loads of this position are issued eight at a time before their first use (the compiler otherwise
+            // pairs each load with its FMA and keeps two in flight); two batches keep the kernel at three blocks per SM
 #pragma unroll
-            for (int j = 0; j < kKmax; ++j) z[j] = (k0 + j < k) ? __ldcs(Zi + (int64_t)(k0 + j) * ni + t) : 0.0;
+            for (int h = 0; h < kKmax; h += 8) {
+                double z[8];
 #pragma unroll
-            for (int j = 0; j < kKmax; ++j) acc[j] = fma(z[j], v, acc[j]);
+                for (int j = 0; j < 8; ++j) z[j] = (k0 + h + j < k) ? __ldcs(Zi + (int64_t)(k0 + h + j) * ni + t) : 0.0;
+#pragma unroll
+                for (int j = 0; j < 8; ++j) acc[h + j] = fma(z[j], v, acc[h + j]);
+            }
         }
         if (k > 0) {
+            // fixed summation tree: lanes by butterfly, then the eight warps in ascending order; ONE barrier pair for all
+            // basis vectors of the batch
 #pragma unroll
             for (int j = 0; j < kKmax; ++j) {
-                if (k0 + j < k) { // uniform across the block
-                    const double s = block_sum_256(acc[j], sm);
-                    if (threadIdx.x == 0) partial[(int64_t)blockIdx.x * kpad + k0 + j] = s;
-                }
+                double s = acc[j];
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(kFull, s, o);
+                if (lane == 0) sm[warp][j] = s;
             }
+            __syncthreads();
+            if (threadIdx.x < kKmax && k0 + (int)threadIdx.x < k) {
+                double s = 0.0;
+#pragma unroll
+                for (int w = 0; w < 8; ++w) s += sm[w][threadIdx.x];
+                partial[(int64_t)blockIdx.x * kpad + k0 + threadIdx.x] = s;
+            }
+            __syncthreads();
         }
     }
 }
