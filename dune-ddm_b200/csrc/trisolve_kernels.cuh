@@ -6,8 +6,15 @@ namespace ddm {
 // forward sweep: WX[rows] += panel(rows, chunks) * y(chunks)   (the panel holds D^{-1} rows and -Lt rows)
 // Per task the vector operand (<= kGroup chunks of y) and the row targets are staged once in shared memory, so the
 // tile loop touches shared memory only; the next ticket and descriptor are fetched while the tiles are consumed.
-__global__ void __launch_bounds__(kTriWarps * 32, 1) trisolve_fwd_kernel(const TriTask *__restrict__ tasks, int ntasks, double *WX,
-                                                                          int *cnt, int *ticket, int xoff)
+//
+// DET = true is the reproducible variant (ddm_set_deterministic): no floating-point atomics.  Every task stores its results
+// into private slots of S (its row targets are slot numbers), and "assemble" tasks (ntiles == 0), one per 32-column chunk of
+// every supernode that has children, add the slots that belong to their columns in ascending slot number -- a fixed order
+// -- before the supernode's compute tasks read y.  The default variant (DET = false) is the code as it was.
+template <bool DET>
+__global__ void __launch_bounds__(kTriWarps * 32, 1) trisolve_fwd_kernel_t(const TriTask *__restrict__ tasks, int ntasks, double *WX,
+                                                                            int *cnt, int *ticket, int xoff, double *__restrict__ S,
+                                                                            const int32_t *__restrict__ lptr, const int32_t *__restrict__ lidx)
 {
     extern __shared__ __align__(128) unsigned char tri_smem[];
     TriWarp w;
@@ -17,6 +24,22 @@ __global__ void __launch_bounds__(kTriWarps * 32, 1) trisolve_fwd_kernel(const T
     while (w.hasA) {
         const int ncc = w.A.ncc;
         w.prefetch_ticket();
+        if (DET && w.A.ntiles == 0) {
+            // assemble y for 32 columns: restricted defect + the descendants' contributions, in slot order
+            if (w.A.wait_cnt >= 0) wait_counter(cnt + w.A.wait_cnt, w.A.wait_need, lane);
+            w.prefetch_task();
+            if (lane < w.A.w) {
+                const int p = w.A.vec + lane;
+                double y = __ldcg(WX + p);
+                for (int q = lptr[p]; q < lptr[p + 1]; ++q) y += __ldcg(S + lidx[q]);
+                WX[p] = y;
+            }
+            __threadfence();
+            __syncwarp();
+            if (lane == 0) atomicAdd(cnt + w.A.signal_cnt, 1);
+            w.advance();
+            continue;
+        }
         if (ncc == 0) {
             // Symmetric task on the inverse diagonal block: tiles (r, c) of its lower triangle, fixed chunk c.  Each tile
             // is used twice: z_r += T y_c, and (off the diagonal) z_c += T^T y_r -- the upper triangle is never stored.
@@ -60,7 +83,10 @@ __global__ void __launch_bounds__(kTriWarps * 32, 1) trisolve_fwd_kernel(const T
                         }
                 }
                 w.release_tile();
-                if (ti * 32 + lane < nvalid) atomicAdd(zr + (k0 + ti) * 32, a0 + a1);
+                if (DET) {
+                    if (ti * 32 + lane < nvalid) S[w.A.signal_cnt + ti * 32 + lane] = a0 + a1;  // symmetric tasks carry their slot base here
+                } else if (ti * 32 + lane < nvalid)
+                    atomicAdd(zr + (k0 + ti) * 32, a0 + a1);
             }
 #pragma unroll
             for (int half = 16; half >= 1; half >>= 1) {
@@ -72,7 +98,10 @@ __global__ void __launch_bounds__(kTriWarps * 32, 1) trisolve_fwd_kernel(const T
                     acc[k] = keep + __shfl_xor_sync(kFull, send, half);
                 }
             }
-            if (lane < wc) atomicAdd(zr, acc[0]);
+            if (DET) {
+                if (lane < wc) S[w.A.signal_cnt + nt * 32 + lane] = acc[0];
+            } else if (lane < wc)
+                atomicAdd(zr, acc[0]);
             w.advance();  // nobody waits for the diagonal block: no fence, no signal
             continue;
         }
@@ -115,7 +144,10 @@ __global__ void __launch_bounds__(kTriWarps * 32, 1) trisolve_fwd_kernel(const T
                 w.release_tile();
             }
             const int tgt = w.idx[g * 32 + lane];
-            if (tgt >= 0) atomicAdd(WX + tgt, (a0 + a1) + (a2 + a3));
+            if (DET) {
+                if (tgt >= 0) S[tgt] = (a0 + a1) + (a2 + a3);  // row targets are slot numbers
+            } else if (tgt >= 0)
+                atomicAdd(WX + tgt, (a0 + a1) + (a2 + a3));
         }
         if (w.A.signal_cnt >= 0) {  // somebody waits for this task: publish the accumulations, then count
             __threadfence();
@@ -129,8 +161,12 @@ __global__ void __launch_bounds__(kTriWarps * 32, 1) trisolve_fwd_kernel(const T
 // backward sweep: WX[cols] += panel(rows, cols)^T * x(rows)   (the panel holds -Lt)
 // The row lists (static) are fetched before the dependency wait, all x gathers of the task are issued together
 // after it and staged in shared memory.
-__global__ void __launch_bounds__(kTriWarps * 32, 1) trisolve_bwd_kernel(const TriTask *__restrict__ tasks, int ntasks, double *WX,
-                                                                          int *cnt, int *ticket, int xoff)
+// DET: compute tasks store their 32 partial sums into the slots at S[gstride ..]; assemble tasks (ntiles == 0), one per column
+// chunk of every supernode, form x = (z slots of the forward sweep) + (slots of this supernode's backward tasks), in slot order.
+template <bool DET>
+__global__ void __launch_bounds__(kTriWarps * 32, 1) trisolve_bwd_kernel_t(const TriTask *__restrict__ tasks, int ntasks, double *WX,
+                                                                            int *cnt, int *ticket, int xoff, double *__restrict__ S,
+                                                                            const int32_t *__restrict__ lptr, const int32_t *__restrict__ lidx)
 {
     extern __shared__ __align__(128) unsigned char tri_smem[];
     TriWarp w;
@@ -141,6 +177,21 @@ __global__ void __launch_bounds__(kTriWarps * 32, 1) trisolve_bwd_kernel(const T
         const int nt = w.A.ntiles;
         const int wc = w.A.w;
         w.prefetch_ticket();
+        if (DET && nt == 0) {
+            if (w.A.wait_cnt >= 0) wait_counter(cnt + w.A.wait_cnt, w.A.wait_need, lane);
+            w.prefetch_task();
+            if (lane < wc) {
+                const int p = w.A.vec + lane - xoff;  // list index = position inside X
+                double x = 0.0;
+                for (int q = lptr[p]; q < lptr[p + 1]; ++q) x += __ldcg(S + lidx[q]);
+                WX[w.A.vec + lane] = x;
+            }
+            __threadfence();
+            __syncwarp();
+            if (lane == 0) atomicAdd(cnt + w.A.signal_cnt, 1);
+            w.advance();
+            continue;
+        }
         int rr[kGroup];
 #pragma unroll
         for (int t = 0; t < kGroup; ++t) rr[t] = (t < nt) ? __ldg(w.A.rowidx + t * 32 + lane) : -1;
@@ -179,7 +230,10 @@ __global__ void __launch_bounds__(kTriWarps * 32, 1) trisolve_bwd_kernel(const T
                 acc[k] = keep + __shfl_xor_sync(kFull, send, half);
             }
         }
-        if (lane < wc) atomicAdd(WX + w.A.vec + lane, acc[0]);
+        if (DET) {
+            if (lane < wc) S[w.A.gstride + lane] = acc[0];
+        } else if (lane < wc)
+            atomicAdd(WX + w.A.vec + lane, acc[0]);
         if (w.A.signal_cnt >= 0) {  // somebody waits for this task: publish the accumulations, then count
             __threadfence();
             __syncwarp();
@@ -188,6 +242,12 @@ __global__ void __launch_bounds__(kTriWarps * 32, 1) trisolve_bwd_kernel(const T
         w.advance();
     }
 }
+
+// the two instantiations of each sweep under the names the host code launches
+#define trisolve_fwd_kernel trisolve_fwd_kernel_t<false>
+#define trisolve_bwd_kernel trisolve_bwd_kernel_t<false>
+#define trisolve_fwd_det_kernel trisolve_fwd_kernel_t<true>
+#define trisolve_bwd_det_kernel trisolve_bwd_kernel_t<true>
 
 // ---- setup-time conversion: column-major sources -> tiles --------------------------------------------------
 // kind 0: tile = -(rows of the raw panel) * Linv  (Linv: w x w lower, column-major; small supernodes, w <= 32)

@@ -54,3 +54,14 @@ def pytest_collection_modifyitems(config, items):
     for item in items:
         if item.get_closest_marker("gpu") and not item.get_closest_marker("timeout"):
             item.add_marker(pytest.mark.timeout(900, method="thread"))
+
+
+@pytest.fixture(autouse=True)
+def _gpu_tests_run_on_the_real_library(request):
+    """Every `-m gpu` test must exercise libddm_b200.so itself: the dry-run stand-in (tests/dryrun_standin.py, an opt-in
+    proof-reading plugin that answers the C ABI from the oracle) reports version b"dryrun" and must never count as GPU coverage."""
+    if request.node.get_closest_marker("gpu") and not request.config.pluginmanager.hasplugin("dryrun_standin"):
+        from ddm_b200 import lib
+
+        assert b"dryrun" not in lib.load().ddm_version(), "GPU test running on the dry-run stand-in"
+    yield
