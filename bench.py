@@ -60,6 +60,7 @@ def parse():
     ap.add_argument("--nev-max", type=int, default=None)
     ap.add_argument("--cpu-seconds", type=float, default=20.0, help="budget of the cpu_baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--deterministic", action="store_true", help="reproducible sweeps (ddm_set_deterministic): no floating-point atomics")
     ap.add_argument("--pack", default=None, help=".ddmpack cache of the setup products (global setup only)")
     ap.add_argument("--strong", action="store_true", help="strong scaling: the N = 1 problem split over the GPUs")
     ap.add_argument("--setup-only", action="store_true")
@@ -441,10 +442,10 @@ def run_b200(a):
         dist.broadcast(t, 0)
         uid = t.tolist()
     if L is not None:
-        ctx = api.Context.from_local(L, device=local, unique_id=uid, keep_A0=(world == 1 and not a.no_cpu_baseline))
+        ctx = api.Context.from_local(L, device=local, unique_id=uid, keep_A0=(world == 1 and not a.no_cpu_baseline), deterministic=a.deterministic)
         b_own = L.b_own
     else:
-        ctx = api.Context.from_products(P, device=local, rank=rank, world=world, unique_id=uid)
+        ctx = api.Context.from_products(P, device=local, rank=rank, world=world, unique_id=uid, deterministic=a.deterministic)
         b_own = ctx.owned(P.b)
     t_upload = time.perf_counter() - t0
     if rank == 0:
@@ -576,7 +577,7 @@ def run_b200(a):
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": a.warmup, "ms_per_step": ms_step,
         "higher_is_better": True, "scaling": "strong" if a.strong else "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "config": config_of(a, world, n, nsub, N0),
-        "iterations": int(res.iterations), "converged": bool(res.converged), "factor_nnz": stats["factor_nnz"],
+        "iterations": int(res.iterations), "converged": bool(res.converged), "factor_nnz": stats["factor_nnz"], "deterministic_sweeps": bool(a.deterministic),
         "parity": {"true_residual": true_res, "bound": 1.05 * REDUCTION, "iterations_equal_on_all_ranks": same_its, "oracle_iterations": None},
         "time_to_1e-8_s": ms_step * 1e-3, "wall_ms_per_step": t_wall / a.steps * 1e3,
         "setup_s": {"host": t_setup, "upload_and_device_setup": t_upload},

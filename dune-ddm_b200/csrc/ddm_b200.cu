@@ -184,6 +184,10 @@ struct ddm_ctx {
     int32_t n_fwd = 0, n_bwd = 0, nsn = 0;
     int *cnt = nullptr; // [2*nsn + 2]: fwd counters, bwd counters, tickets
     int tri_grid = 0;
+    size_t cnt_ints = 0;
+    bool deterministic = false;  // ddm_set_deterministic: sweeps without floating-point atomics (slots + assemble tasks)
+    double *det_S = nullptr;
+    int32_t *det_rows = nullptr, *det_lf_ptr = nullptr, *det_lf_idx = nullptr, *det_lx_ptr = nullptr, *det_lx_idx = nullptr;
     cublasHandle_t blas = nullptr;
     cusolverDnHandle_t solver = nullptr;
     double *mf_arena = nullptr;  // update matrices of the device factorisation (setup scratch, released by ddm_finalize)
@@ -338,7 +342,8 @@ extern "C" int ddm_ctx_destroy(ddm_ctx *c)
     void *ptrs[] = {c->Linv, c->rowptr, c->col, c->val, c->A0, c->A0inv, c->d0, c->y0, c->r0, c->gidx, c->pouP, c->Zp, c->W,
                     c->zoff, c->d_sub_n, c->d_sub_k, c->d_koff, c->seg_ptr, c->segs, c->cpartial, c->dptr, c->dpos,
                     c->fwd_tasks, c->bwd_tasks, c->cnt, c->partial, c->scal, c->send_idx, c->sendbuf,
-                    c->recvbuf, c->rev_tgt, c->rev_ptr, c->rev_pos, c->sell_ptr, c->sell_col, c->sell_val};
+                    c->recvbuf, c->rev_tgt, c->rev_ptr, c->rev_pos, c->sell_ptr, c->sell_col, c->sell_val, c->det_S, c->det_rows,
+                    c->det_lf_ptr, c->det_lf_idx, c->det_lx_ptr, c->det_lx_idx};
     for (void *p : ptrs) cudaFree(p);
     cudaFreeHost(c->h_scal);
     cudaFreeHost(c->h_stage);
@@ -1253,6 +1258,17 @@ extern "C" int ddm_upload_coarse(ddm_ctx *c, const int32_t *k, const double *Z, 
 // ------------------------------------------------------------------------------------------------ finalize
 extern "C" int ddm_vec_create(ddm_ctx *c, ddm_vec **out);
 
+// Reproducible triangular sweeps: results are bit-identical run to run (no floating-point atomics).  Takes effect at the
+// next ddm_finalize.
+extern "C" int ddm_set_deterministic(ddm_ctx *c, int on)
+{
+    if (c->deterministic != (on != 0)) {
+        c->deterministic = on != 0;
+        c->finalized = false;
+    }
+    return 0;
+}
+
 extern "C" int ddm_finalize(ddm_ctx *c)
 {
     CU(cudaSetDevice(c->device));
@@ -1362,6 +1378,7 @@ extern "C" int ddm_finalize(ddm_ctx *c)
         int32_t level, sub, J, kind /* 0 below, 1 diag (fwd) */, a, b;  // fwd: row tile a, chunk group b; bwd: chunk a, row group b
     };
     std::vector<Key> fkeys, bkeys;
+    std::vector<std::vector<int32_t>> rabs_all(c->deterministic ? ns : 0);  // absolute row targets per subdomain (deterministic schedule)
     double bytes_stored = 0, bytes_alg = 0, bytes_below = 0;
     for (int32_t i = 0; i < ns; ++i) {
         SubFactor &F = c->fac[i];
@@ -1374,6 +1391,7 @@ extern "C" int ddm_finalize(ddm_ctx *c)
         cudaFree(F.rowidx);
         F.rowidx = nullptr;
         CK(dev_upload(&F.rowidx, rabs.data(), rabs.size()));
+        if (c->deterministic) rabs_all[i] = rabs;
         const int32_t nsn = (int32_t)F.cw.size();
         for (int32_t J = 0; J < nsn; ++J) {
             const int32_t cw = F.cw[J], nb = F.nb[J];
@@ -1510,13 +1528,165 @@ extern "C" int ddm_finalize(ddm_ctx *c)
         t.signal_cnt = haschild[sn_base[k.sub] + k.J] ? c->nsn + sn_base[k.sub] + k.J : -1;  // leaves: nobody waits
         bwd.push_back(t);
     }
+    c->cnt_ints = 2 * (size_t)c->nsn + 2;
+    for (void *p : {(void *)c->det_S, (void *)c->det_rows, (void *)c->det_lf_ptr, (void *)c->det_lf_idx, (void *)c->det_lx_ptr, (void *)c->det_lx_idx}) cudaFree(p);
+    c->det_S = nullptr;
+    c->det_rows = c->det_lf_ptr = c->det_lf_idx = c->det_lx_ptr = c->det_lx_idx = nullptr;
+    if (c->deterministic) {
+        // Reproducible sweeps (trisolve_kernels.cuh, DET = true): every task result goes to a private slot, "assemble" tasks
+        // sum the slots of their columns in ascending slot number.  Counters: [0,nsn) forward compute, [nsn,2nsn) backward
+        // compute, 2 tickets, then [AF, AF+nsn) forward assemble done, [AB, AB+nsn) backward assemble done.
+        const int32_t nsn_all = c->nsn, AF = 2 * nsn_all + 2, AB = 3 * nsn_all + 2;
+        c->cnt_ints = 4 * (size_t)nsn_all + 2;
+        std::vector<int32_t> ncc_of(nsn_all), lvl_of(nsn_all), col_of(nsn_all), cw_of(nsn_all);
+        int32_t maxlvl = 0;
+        for (int32_t i = 0; i < ns; ++i) {
+            const SubFactor &F = c->fac[i];
+            for (size_t J = 0; J < F.cw.size(); ++J) {
+                const int32_t gs = sn_base[i] + (int32_t)J;
+                ncc_of[gs] = (F.cw[J] + 31) / 32;
+                lvl_of[gs] = F.level[J];
+                col_of[gs] = (int32_t)(c->sub_ptr[i] + F.col0[J]);
+                cw_of[gs] = F.cw[J];
+                maxlvl = std::max(maxlvl, F.level[J]);
+            }
+        }
+        std::vector<std::vector<int32_t>> by_lvl(maxlvl + 1);
+        for (int32_t gs = 0; gs < nsn_all; ++gs) by_lvl[lvl_of[gs]].push_back(gs);
+        int64_t nslot = 0;
+        std::vector<int32_t> det_rows;                            // slot numbers per (forward task, row), -1 = padding
+        std::vector<std::pair<int32_t, int32_t>> pw, px;          // (position in W / in X, slot), ascending slot
+        std::vector<int64_t> rows_off;                            // per forward task of fwd2: offset into det_rows (-1: none)
+        std::vector<TriTask> fwd2, bwd2;
+        auto assemble = [&](int32_t gs, int32_t cc, bool fwd_sweep) {
+            TriTask t;
+            t.tiles = nullptr;
+            t.rowidx = nullptr;
+            t.stride = 0;
+            t.gstride = 0;
+            t.ntiles = 0;
+            t.ncc = 1;
+            t.w = t.wlast = (int16_t)std::min(32, cw_of[gs] - cc * 32);
+            if (fwd_sweep) {
+                t.vec = col_of[gs] + cc * 32;
+                t.wait_cnt = need[gs] > 0 ? gs : -1;
+                t.wait_need = need[gs];
+                t.signal_cnt = AF + gs;
+            } else {
+                t.vec = (int32_t)(P + col_of[gs] + cc * 32);
+                t.wait_cnt = nbwd[gs] > 0 ? nsn_all + gs : -1;
+                t.wait_need = nbwd[gs];
+                t.signal_cnt = AB + gs;
+            }
+            return t;
+        };
+        // ---- forward: per level the assemble tasks (supernodes with children), then the compute tasks in their old order
+        size_t q = 0;
+        for (int32_t l = 0; l <= maxlvl; ++l) {
+            for (int32_t gs : by_lvl[l])
+                if (haschild[gs])
+                    for (int32_t cc = 0; cc < ncc_of[gs]; ++cc) {
+                        fwd2.push_back(assemble(gs, cc, true));
+                        rows_off.push_back(-1);
+                    }
+            for (; q < fkeys.size() && fkeys[q].level == l; ++q) {
+                const Key &k = fkeys[q];
+                const SubFactor &F = c->fac[k.sub];
+                const int32_t gs = sn_base[k.sub] + k.J;
+                TriTask t = fwd[q];
+                if (haschild[gs]) {
+                    t.wait_cnt = AF + gs;
+                    t.wait_need = ncc_of[gs];
+                } else {
+                    t.wait_cnt = -1;
+                    t.wait_need = 0;
+                }
+                if (t.ncc == 0) {  // symmetric diagonal task: nt row tiles + its column chunk, slot base travels in signal_cnt
+                    const int32_t cc = k.a, r0 = k.b, nt = t.ntiles, wc = t.w, nvalid = t.gstride;
+                    if (nslot + (int64_t)(nt + 1) * 32 >= INT32_MAX) return fail("deterministic schedule: too many slots");
+                    t.signal_cnt = (int32_t)nslot;
+                    const int32_t xb = (int32_t)(P + col_of[gs]);
+                    for (int32_t ti = 0; ti < nt; ++ti)
+                        for (int32_t ln = 0; ln < 32; ++ln)
+                            if (ti * 32 + ln < nvalid) px.push_back({xb + (r0 + ti) * 32 + ln - (int32_t)P, (int32_t)(nslot + ti * 32 + ln)});
+                    for (int32_t ln = 0; ln < wc; ++ln) px.push_back({xb + cc * 32 + ln - (int32_t)P, (int32_t)(nslot + nt * 32 + ln)});
+                    nslot += (int64_t)(nt + 1) * 32;
+                    rows_off.push_back(-1);
+                } else {
+                    const int32_t ng = t.ntiles / t.ncc;
+                    const int64_t off0 = t.rowidx - F.rowidx;
+                    rows_off.push_back((int64_t)det_rows.size());
+                    for (int32_t g = 0; g < ng; ++g)
+                        for (int32_t ln = 0; ln < 32; ++ln) {
+                            const int32_t tgt = rabs_all[k.sub][off0 + (int64_t)g * 32 + ln];
+                            if (tgt < 0) {
+                                det_rows.push_back(-1);
+                                continue;
+                            }
+                            if (nslot >= INT32_MAX) return fail("deterministic schedule: too many slots");
+                            det_rows.push_back((int32_t)nslot);
+                            if (tgt < P) pw.push_back({tgt, (int32_t)nslot});
+                            else px.push_back({tgt - (int32_t)P, (int32_t)nslot});
+                            ++nslot;
+                        }
+                }
+                fwd2.push_back(t);
+            }
+        }
+        // ---- backward: per level (descending) the compute tasks, then the assemble tasks of that level's supernodes
+        q = 0;
+        for (int32_t l = maxlvl; l >= 0; --l) {
+            for (; q < bkeys.size() && bkeys[q].level == l; ++q) {
+                const Key &k = bkeys[q];
+                const SubFactor &F = c->fac[k.sub];
+                const int32_t gs = sn_base[k.sub] + k.J, par = sn_base[k.sub] + F.parent[k.J];
+                TriTask t = bwd[q];
+                t.wait_cnt = AB + par;
+                t.wait_need = ncc_of[par];
+                t.signal_cnt = nsn_all + gs;
+                if (nslot + 32 >= INT32_MAX) return fail("deterministic schedule: too many slots");
+                t.gstride = (int32_t)nslot;
+                for (int32_t ln = 0; ln < t.w; ++ln) px.push_back({t.vec - (int32_t)P + ln, (int32_t)(nslot + ln)});
+                nslot += 32;
+                bwd2.push_back(t);
+            }
+            for (int32_t gs : by_lvl[l])
+                for (int32_t cc = 0; cc < ncc_of[gs]; ++cc) bwd2.push_back(assemble(gs, cc, false));
+        }
+        // ---- lists by target, ascending slot inside a list (the pairs were generated in ascending slot order)
+        auto lists = [&](const std::vector<std::pair<int32_t, int32_t>> &pairs, std::vector<int32_t> &ptr, std::vector<int32_t> &idx) {
+            ptr.assign((size_t)P + 1, 0);
+            for (const auto &pr : pairs) ptr[(size_t)pr.first + 1]++;
+            for (int64_t p = 0; p < P; ++p) ptr[p + 1] += ptr[p];
+            idx.resize(pairs.size());
+            std::vector<int32_t> fill(ptr.begin(), ptr.end() - 1);
+            for (const auto &pr : pairs) idx[fill[pr.first]++] = pr.second;
+        };
+        if (pw.size() >= (size_t)INT32_MAX || px.size() >= (size_t)INT32_MAX) return fail("deterministic schedule: lists too long");
+        std::vector<int32_t> lf_ptr, lf_idx, lx_ptr, lx_idx;
+        lists(pw, lf_ptr, lf_idx);
+        lists(px, lx_ptr, lx_idx);
+        CK(dev_upload(&c->det_rows, det_rows.data(), det_rows.size()));
+        CK(dev_upload(&c->det_lf_ptr, lf_ptr.data(), lf_ptr.size()));
+        CK(dev_upload(&c->det_lf_idx, lf_idx.data(), lf_idx.size()));
+        CK(dev_upload(&c->det_lx_ptr, lx_ptr.data(), lx_ptr.size()));
+        CK(dev_upload(&c->det_lx_idx, lx_idx.data(), lx_idx.size()));
+        CU(cudaMalloc((void **)&c->det_S, sizeof(double) * std::max<int64_t>(1, nslot)));
+        for (size_t t = 0; t < fwd2.size(); ++t)
+            if (rows_off[t] >= 0) fwd2[t].rowidx = c->det_rows + rows_off[t];
+        fwd.swap(fwd2);
+        bwd.swap(bwd2);
+        c->stats["det_slots"] = (double)nslot;
+    }
     c->n_fwd = (int32_t)fwd.size();
     c->n_bwd = (int32_t)bwd.size();
     CK(dev_upload(&c->fwd_tasks, fwd.data(), fwd.size()));
     CK(dev_upload(&c->bwd_tasks, bwd.data(), bwd.size()));
-    CU(cudaMalloc((void **)&c->cnt, sizeof(int) * (2 * (size_t)c->nsn + 2)));
+    CU(cudaMalloc((void **)&c->cnt, sizeof(int) * c->cnt_ints));
     CU(cudaFuncSetAttribute(trisolve_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kTriSmemBytes));
     CU(cudaFuncSetAttribute(trisolve_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kTriSmemBytes));
+    CU(cudaFuncSetAttribute(trisolve_fwd_det_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kTriSmemBytes));
+    CU(cudaFuncSetAttribute(trisolve_bwd_det_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kTriSmemBytes));
     int bps_f = 0, bps_b = 0;
     CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps_f, trisolve_fwd_kernel, kTriWarps * 32, kTriSmemBytes));
     CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps_b, trisolve_bwd_kernel, kTriWarps * 32, kTriSmemBytes));
@@ -1714,20 +1884,23 @@ static int coarse_solve(ddm_ctx *c, cudaStream_t st = nullptr)
 static int trisolve(ddm_ctx *c)
 {
     ScopedTimer tm(c, "Schwarz/local solve");
-    CU(cudaMemsetAsync(c->cnt, 0, sizeof(int) * (2 * (size_t)c->nsn + 2), c->s));
+    CU(cudaMemsetAsync(c->cnt, 0, sizeof(int) * c->cnt_ints, c->s));
     int *cnt = c->cnt, *tick_f = c->cnt + 2 * c->nsn, *tick_b = tick_f + 1;
+    const bool det = c->deterministic;
     {
         ScopedTimer tf(c, "Schwarz/local solve fwd");
         int xoff = (int)c->P;
-        void *args[] = {&c->fwd_tasks, &c->n_fwd, &c->W, &cnt, &tick_f, &xoff};
-        CU(cudaLaunchCooperativeKernel((void *)trisolve_fwd_kernel, dim3(c->tri_grid), dim3(kTriWarps * 32), args, kTriSmemBytes, c->s));
+        void *args[] = {&c->fwd_tasks, &c->n_fwd, &c->W, &cnt, &tick_f, &xoff, &c->det_S, &c->det_lf_ptr, &c->det_lf_idx};
+        CU(cudaLaunchCooperativeKernel(det ? (void *)trisolve_fwd_det_kernel : (void *)trisolve_fwd_kernel, dim3(c->tri_grid), dim3(kTriWarps * 32), args,
+                                       kTriSmemBytes, c->s));
         c->launches++;
     }
     if (c->n_bwd > 0) {
         ScopedTimer tb(c, "Schwarz/local solve bwd");
         int xoff = (int)c->P;
-        void *args[] = {&c->bwd_tasks, &c->n_bwd, &c->W, &cnt, &tick_b, &xoff};
-        CU(cudaLaunchCooperativeKernel((void *)trisolve_bwd_kernel, dim3(c->tri_grid), dim3(kTriWarps * 32), args, kTriSmemBytes, c->s));
+        void *args[] = {&c->bwd_tasks, &c->n_bwd, &c->W, &cnt, &tick_b, &xoff, &c->det_S, &c->det_lx_ptr, &c->det_lx_idx};
+        CU(cudaLaunchCooperativeKernel(det ? (void *)trisolve_bwd_det_kernel : (void *)trisolve_bwd_kernel, dim3(c->tri_grid), dim3(kTriWarps * 32), args,
+                                       kTriSmemBytes, c->s));
         c->launches++;
     }
     return 0;

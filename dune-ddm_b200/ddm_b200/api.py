@@ -88,7 +88,8 @@ class Context:
         self.world = 1
 
     @classmethod
-    def from_products(cls, P, device=0, rank=0, world=1, unique_id=None, with_coarse=True, device_galerkin=False, with_pou=True):
+    def from_products(cls, P, device=0, rank=0, world=1, unique_id=None, with_coarse=True, device_galerkin=False, with_pou=True,
+                      deterministic=False):
         """Upload the setup products (whole problem, or this rank's shard).  device_galerkin: do not upload P.A0 but
         assemble Z^T A Z on the GPU (ddm_galerkin_assemble); the result is kept in self.A0_device.  with_pou=False uploads no
         partition of unity: restricted Schwarz then applies no weights (schwarz.hh:140, pou == nullptr)."""
@@ -96,22 +97,25 @@ class Context:
         a, b = S.sub_range
         N0 = int(P.A0.shape[0])
         return cls._from_shard(S, [P.pou[i] for i in range(a, b)], [P.factors[i] for i in range(a, b)], [P.Z[i] for i in range(a, b)],
-                               N0, P.A0, device, unique_id, with_coarse, device_galerkin, with_pou, block=P.meta.get("block"))
+                               N0, P.A0, device, unique_id, with_coarse, device_galerkin, with_pou, block=P.meta.get("block"),
+                               deterministic=deterministic)
 
     @classmethod
-    def from_local(cls, L, device=0, unique_id=None, with_coarse=True, with_pou=True, keep_A0=False):
+    def from_local(cls, L, device=0, unique_id=None, with_coarse=True, with_pou=True, keep_A0=False, deterministic=False):
         """Upload one rank's own products (setup.local.LocalProducts: nothing global exists on any rank).  L.k_all must hold
         the coarse-vector counts of all subdomains of the job; the Galerkin matrix is assembled on the devices."""
         S = L.shard
         k_all = np.asarray(L.k_all, dtype=np.int64)
         S.k_offset = int(k_all[: S.sub_range[0]].sum())
         return cls._from_shard(S, L.pou, L.factors, L.Z, int(k_all.sum()), None, device, unique_id, with_coarse, True, with_pou,
-                               keep_A0=keep_A0)
+                               keep_A0=keep_A0, deterministic=deterministic)
 
     @classmethod
     def _from_shard(cls, S, pou_list, factors, Z_list, N0, A0, device, unique_id, with_coarse, device_galerkin, with_pou, block=None,
-                    keep_A0=True):
+                    keep_A0=True, deterministic=False):
         self = cls(device)
+        if deterministic:  # reproducible sweeps (no floating-point atomics): schedules are built accordingly by ddm_finalize
+            check(self.lib.ddm_set_deterministic(self.h, C.c_int(1)))
         rank, world = S.rank, S.world
         self.shard, self.world, self.rank = S, world, rank
         lib = self.lib

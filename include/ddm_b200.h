@@ -124,6 +124,12 @@ int ddm_factorize_subdomain(ddm_ctx *ctx, int32_t sub, int32_t n, int32_t nsuper
 int ddm_upload_coarse(ddm_ctx *ctx, const int32_t *k, const double *Z, int32_t N0, int32_t k_offset,
                       const double *A0);
 
+/* Reproducible subdomain solves (optional, before ddm_finalize): the triangular sweeps then use no floating-point atomics --
+ * every task result goes to a private slot and per-supernode "assemble" tasks add the slots in a fixed order -- so that two
+ * runs give bit-identical results, as cholmod_l_solve does on one rank (extern/dune-istl/dune/istl/cholmod.hh:293).  Costs a
+ * few percent of sweep time and 12 bytes per stored factor row; the default (off) accumulates with FP64 atomics. */
+int ddm_set_deterministic(ddm_ctx *ctx, int on);
+
 /* Builds the device schedules; call after all uploads. */
 int ddm_finalize(ddm_ctx *ctx);
 

@@ -1,0 +1,82 @@
+"""Reproducible sweeps (ddm_set_deterministic): two applications of the preconditioner give bit-identical vectors, two PCG
+solves identical defect histories, and the results agree with the default (atomic) sweeps and with the oracle.  The reference's
+cholmod_l_solve is deterministic per rank (extern/dune-istl/dune/istl/cholmod.hh:293); SURVEY 7.3(6) asks the same of this path."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+def rel(a, b):
+    return np.linalg.norm(a - b) / max(np.linalg.norm(b), 1e-300)
+
+
+@pytest.fixture(scope="module")
+def brick():
+    from ddm_b200.setup import problem
+
+    return problem.poisson_q1_cube(24, (2, 2, 2), overlap=2, coarse="pou", workers=1)  # wide supernodes: symmetric diagonal tasks
+
+
+def _prec(api, ctx, typ="standard", mode="additive"):
+    op = api.NonOverlappingOperator(ctx)
+    C = api.CombinedPreconditioner(mode)
+    C.set_op(op)
+    C.add(api.SchwarzPreconditioner(ctx, typ))
+    C.add(api.GalerkinPreconditioner(ctx))
+    return op, C
+
+
+@pytest.mark.parametrize("name", ["small3d", "small2d", "brick", "cd_dg"])
+def test_deterministic_sweeps_are_bit_reproducible_and_correct(request, name):
+    from ddm_b200 import api
+    from oracle import oracle
+
+    P = request.getfixturevalue(name)
+    typ, mode = ("restricted", "multiplicative") if name == "cd_dg" else ("standard", "additive")
+    ctx = api.Context.from_products(P, deterministic=True)
+    assert ctx.stat("det_slots") > 0
+    op, C = _prec(api, ctx, typ, mode)
+    rng = np.random.default_rng(3)
+    d = rng.standard_normal(P.n)
+    runs = [C.apply_host(d) for _ in range(4)]
+    for r in runs[1:]:
+        assert np.array_equal(r, runs[0])  # bit for bit
+    O = oracle.Oracle(P, nthreads=4)
+    want = O.twolevel_apply(d, restricted=typ == "restricted", mode=mode)
+    kap = np.linalg.cond(P.A0)
+    assert rel(runs[0], want) <= max(1e-12, 8 * np.finfo(float).eps * max(kap, 1e8 if name == "small2d" else 1.0))
+    ctx2 = api.Context.from_products(P)  # default sweeps (FP64 atomics): same numbers up to summation order
+    _, C2 = _prec(api, ctx2, typ, mode)
+    assert rel(C2.apply_host(d), runs[0]) <= (1e-10 if name == "small2d" else 1e-13)
+    if name != "cd_dg":
+        sp = api.NonOverlappingScalarProduct(ctx)
+        cg = api.CGSolver(op, sp, C, reduction=1e-8, maxit=200)
+        (x1, r1), (x2, r2) = cg.solve_host(P.b), cg.solve_host(P.b)
+        assert r1.converged and np.array_equal(x1, x2) and np.array_equal(r1.history, r2.history)
+        xo, ito, _, _ = O.pcg(P.b, reduction=1e-8, maxit=200)
+        assert abs(r1.iterations - ito) <= 1 and rel(x1, xo) <= 1e-8
+    ctx.close()
+    ctx2.close()
+
+
+def test_deterministic_mode_with_device_factorisation(brick):
+    import copy
+
+    from ddm_b200 import api
+    from ddm_b200.setup import factor
+
+    Q = copy.copy(brick)
+    Q.factors = []
+    for s in brick.subs:
+        Ai = brick.A[s][:, s].tocsr()
+        Ai.sort_indices()
+        Q.factors.append(factor.PendingFactor(factor.analyse(Ai, brick.coords[s], 32), Ai))
+    a = api.Context.from_products(Q, deterministic=True)
+    b = api.Context.from_products(Q, deterministic=True)  # a second context, factorised again: the whole chain is reproducible
+    d = np.random.default_rng(9).standard_normal(brick.n)
+    xa = _prec(api, a)[1].apply_host(d)
+    xb = _prec(api, b)[1].apply_host(d)
+    assert np.array_equal(xa, xb)
+    a.close()
+    b.close()
