@@ -165,6 +165,8 @@ struct ddm_ctx {
     std::vector<double> Z_host;
     int32_t N0 = 0, k_offset = 0, kpad = 0;
     bool A0_pending = false;  // coarse basis uploaded without a Galerkin matrix
+    int32_t col_nsub = 0, col_ncolors = 0;  // ddm_set_coarse_coloring: batched Galerkin product
+    std::vector<int32_t> col_color, col_k, col_owner;
     bool coarse_spd = true;   // A0 symmetric: A0inv holds L^{-1} (row-major, lower), Linv holds L^{-T} (row-major, upper)
     double *Linv = nullptr;
     double *A0 = nullptr, *A0inv = nullptr, *d0 = nullptr, *y0 = nullptr, *r0 = nullptr;
@@ -2012,23 +2014,107 @@ extern "C" int ddm_update_coarse_matrix(ddm_ctx *c, const double *A0)
 //   column j = restrict_coarse( A * prolong_coarse(e_j) )
 // (GalerkinPreconditioner::build_solver computes the same entries from A Z_i and neighbour exchanges,
 // dune/ddm/galerkin_preconditioner.hh:246-328).  Works across ranks (halo exchange + all-reduce of each column).
+// Colouring of the subdomains for the Galerkin product (optional): subdomains of one colour are so far apart that no
+// subdomain is coupled (through A) to two of them, so the columns (i, k) of all subdomains i of a colour can be pushed through
+// prolong -> A -> restrict in ONE pass and taken apart afterwards: ncolors x max k_i passes instead of N0.
+// color[nsub_global]; k_global[nsub_global] (basis sizes of all subdomains of the job, global order); owner_of[m * ncolors + c] =
+// the subdomain of colour c coupled to m (m itself included), or -1.
+extern "C" int ddm_set_coarse_coloring(ddm_ctx *c, int32_t nsub_global, int32_t ncolors, const int32_t *color, const int32_t *k_global,
+                                       const int32_t *owner_of)
+{
+    if (nsub_global <= 0 || ncolors <= 0) {
+        c->col_nsub = 0;
+        return 0;
+    }
+    int64_t n0 = 0;
+    for (int32_t i = 0; i < nsub_global; ++i) {
+        if (color[i] < 0 || color[i] >= ncolors) return fail("coarse colouring: colour of subdomain %d out of range", i);
+        n0 += k_global[i];
+    }
+    if (c->N0 > 0 && n0 != c->N0) return fail("coarse colouring: basis sizes sum to %lld, coarse dimension is %d", (long long)n0, c->N0);
+    c->col_nsub = nsub_global;
+    c->col_ncolors = ncolors;
+    c->col_color.assign(color, color + nsub_global);
+    c->col_k.assign(k_global, k_global + nsub_global);
+    c->col_owner.assign(owner_of, owner_of + (size_t)nsub_global * ncolors);
+    return 0;
+}
+
+__global__ void set_ones_kernel(int32_t n, const int32_t *__restrict__ idx, double *__restrict__ y)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) y[idx[i]] = 1.0;
+}
+// after the pass of (colour, k): row r of the coarse residual belongs to column colbase[r] + k of A0 (colbase < 0: no entry)
+__global__ void galerkin_scatter_kernel(int32_t N0, int32_t k, const int32_t *__restrict__ colbase, const int32_t *__restrict__ colk,
+                                        const double *__restrict__ d0, double *__restrict__ A0)
+{
+    const int r = blockIdx.x * blockDim.x + threadIdx.x;
+    if (r < N0 && colbase[r] >= 0 && k < colk[r]) A0[(int64_t)r * N0 + colbase[r] + k] = d0[r];
+}
+
 extern "C" int ddm_galerkin_assemble(ddm_ctx *c, double *A0_out)
 {
     CK(need_final(c));
     const int32_t N0 = c->N0;
     if (N0 <= 0) return fail("no coarse space uploaded");
     double *x = c->tmp[0]->d, *y = c->tmp[1]->d;
-    for (int32_t j = 0; j < N0; ++j) {
-        CU(cudaMemsetAsync(c->y0, 0, sizeof(double) * N0, c->s));
-        LAUNCH(c, fill_kernel, 1, 32, 1, 1.0, c->y0 + j);
+    auto one_pass = [&]() -> int {  // d0 = Z^T A Z y0 over all ranks
         CK(prolong(c, x, 0, 0, 1, 0));
         CK(spmv(c, x, y, 1.0, 0));
         CK(halo_forward(c, y));
         CK(restrict_all(c, y, 1));
-        if (c->nranks > 1) CU(cudaMemsetAsync(c->d0, 0, sizeof(double) * N0, c->s));
-        LAUNCH(c, coarse_restrict_final_kernel, c->nsub, 64, c->nsub, c->seg_ptr, c->d_sub_k, c->d_koff, c->cpartial, c->kpad, c->d0);
-        if (c->nranks > 1) NC(g_nccl.AllReduce(c->d0, c->d0, N0, ncclDouble, ncclSum, c->comm, c->s));
-        CU(cudaMemcpy2DAsync(c->A0 + j, sizeof(double) * N0, c->d0, sizeof(double), sizeof(double), N0, cudaMemcpyDeviceToDevice, c->s));
+        return coarse_gather(c);
+    };
+    if (c->col_nsub > 0) {
+        const int32_t ns = c->col_nsub, nc = c->col_ncolors;
+        std::vector<int32_t> koff(ns + 1, 0);
+        int32_t kmax = 0;
+        for (int32_t i = 0; i < ns; ++i) {
+            koff[i + 1] = koff[i] + c->col_k[i];
+            kmax = std::max(kmax, c->col_k[i]);
+        }
+        DevGuard guard;
+        int32_t *d_idx = nullptr, *d_base = nullptr, *d_colk = nullptr;
+        CU(cudaMalloc((void **)&d_idx, sizeof(int32_t) * ns));
+        guard.own(d_idx);
+        CU(cudaMalloc((void **)&d_base, sizeof(int32_t) * N0));
+        guard.own(d_base);
+        CU(cudaMalloc((void **)&d_colk, sizeof(int32_t) * N0));
+        guard.own(d_colk);
+        CU(cudaMemsetAsync(c->A0, 0, sizeof(double) * (size_t)N0 * N0, c->s));
+        std::vector<int32_t> idx, base(N0), colk(N0);
+        for (int32_t col = 0; col < nc; ++col) {
+            for (int32_t m = 0; m < ns; ++m) {
+                const int32_t o = c->col_owner[(size_t)m * nc + col];
+                for (int32_t r = koff[m]; r < koff[m + 1]; ++r) {
+                    base[r] = o >= 0 ? koff[o] : -1;
+                    colk[r] = o >= 0 ? c->col_k[o] : 0;
+                }
+            }
+            CU(cudaMemcpyAsync(d_base, base.data(), sizeof(int32_t) * N0, cudaMemcpyHostToDevice, c->s));
+            CU(cudaMemcpyAsync(d_colk, colk.data(), sizeof(int32_t) * N0, cudaMemcpyHostToDevice, c->s));
+            for (int32_t k = 0; k < kmax; ++k) {
+                idx.clear();
+                for (int32_t i = 0; i < ns; ++i)
+                    if (c->col_color[i] == col && k < c->col_k[i]) idx.push_back(koff[i] + k);
+                if (idx.empty()) continue;
+                CU(cudaStreamSynchronize(c->s));  // idx / base / colk are reused host buffers
+                CU(cudaMemcpyAsync(d_idx, idx.data(), sizeof(int32_t) * idx.size(), cudaMemcpyHostToDevice, c->s));
+                CU(cudaMemsetAsync(c->y0, 0, sizeof(double) * N0, c->s));
+                LAUNCH(c, set_ones_kernel, nblocks((int64_t)idx.size()), 256, (int32_t)idx.size(), d_idx, c->y0);
+                CK(one_pass());
+                LAUNCH(c, galerkin_scatter_kernel, nblocks(N0), 256, N0, k, d_base, d_colk, c->d0, c->A0);
+            }
+            CU(cudaStreamSynchronize(c->s));
+        }
+    } else {
+        for (int32_t j = 0; j < N0; ++j) {
+            CU(cudaMemsetAsync(c->y0, 0, sizeof(double) * N0, c->s));
+            LAUNCH(c, fill_kernel, 1, 32, 1, 1.0, c->y0 + j);
+            CK(one_pass());
+            CU(cudaMemcpy2DAsync(c->A0 + j, sizeof(double) * N0, c->d0, sizeof(double), sizeof(double), N0, cudaMemcpyDeviceToDevice, c->s));
+        }
     }
     std::vector<double> A0((size_t)N0 * N0);
     CU(cudaMemcpyAsync(A0.data(), c->A0, sizeof(double) * A0.size(), cudaMemcpyDeviceToHost, c->s));

@@ -11,6 +11,7 @@ All arithmetic runs in libddm_b200.so on the GPU; this module only moves pointer
 from __future__ import annotations
 
 import ctypes as C
+import os
 
 import numpy as np
 
@@ -96,9 +97,15 @@ class Context:
         S = shard(P, rank, world)
         a, b = S.sub_range
         N0 = int(P.A0.shape[0])
+        coloring = None
+        if device_galerkin and with_coarse and N0 > 0:  # batched Galerkin product: colours from the coupling graph of the subdomains
+            from .setup import coarse as coarse_mod
+
+            color, ncol, owner = coarse_mod.coupling_coloring(P.A, P.subs)
+            coloring = (color, ncol, owner, np.array([z.shape[1] for z in P.Z], dtype=np.int32))
         return cls._from_shard(S, [P.pou[i] for i in range(a, b)], [P.factors[i] for i in range(a, b)], [P.Z[i] for i in range(a, b)],
                                N0, P.A0, device, unique_id, with_coarse, device_galerkin, with_pou, block=P.meta.get("block"),
-                               deterministic=deterministic)
+                               deterministic=deterministic, coloring=coloring)
 
     @classmethod
     def from_local(cls, L, device=0, unique_id=None, with_coarse=True, with_pou=True, keep_A0=False, deterministic=False):
@@ -107,12 +114,20 @@ class Context:
         S = L.shard
         k_all = np.asarray(L.k_all, dtype=np.int64)
         S.k_offset = int(k_all[: S.sub_range[0]].sum())
+        coloring = None
+        if with_coarse and L.meta.get("pgrid") is not None and min(L.meta["ncell"][ax] // L.meta["pgrid"][ax] for ax in range(3)) > 2 * L.meta["overlap"]:
+            # (bricks wider than twice the overlap: overlapping subdomains two bricks apart share no interior node, so the
+            # Galerkin blocks couple the 26 neighbours only)
+            from .setup import local
+
+            color, ncol, owner = local.brick_coloring(L.meta["pgrid"], L.meta["group"])
+            coloring = (color, ncol, owner, k_all.astype(np.int32))
         return cls._from_shard(S, L.pou, L.factors, L.Z, int(k_all.sum()), None, device, unique_id, with_coarse, True, with_pou,
-                               keep_A0=keep_A0, deterministic=deterministic)
+                               keep_A0=keep_A0, deterministic=deterministic, coloring=coloring)
 
     @classmethod
     def _from_shard(cls, S, pou_list, factors, Z_list, N0, A0, device, unique_id, with_coarse, device_galerkin, with_pou, block=None,
-                    keep_A0=True, deterministic=False):
+                    keep_A0=True, deterministic=False, coloring=None):
         self = cls(device)
         if deterministic:  # reproducible sweeps (no floating-point atomics): schedules are built accordingly by ddm_finalize
             check(self.lib.ddm_set_deterministic(self.h, C.c_int(1)))
@@ -154,6 +169,11 @@ class Context:
             check(lib.ddm_upload_coarse(self.h, _p(k, C.c_int32), _p(np.ascontiguousarray(Z), C.c_double), C.c_int32(N0),
                                         C.c_int32(S.k_offset), None if device_galerkin else _p(A0c, C.c_double)))
         check(lib.ddm_finalize(self.h))
+        if with_coarse and N0 > 0 and device_galerkin and coloring is not None and not os.environ.get("DDM_NO_COLORING"):
+            color, ncol, owner, k_glob = coloring
+            check(lib.ddm_set_coarse_coloring(self.h, C.c_int32(color.size), C.c_int32(ncol), _p(np.ascontiguousarray(color, dtype=np.int32), C.c_int32),
+                                              _p(np.ascontiguousarray(k_glob, dtype=np.int32), C.c_int32),
+                                              _p(np.ascontiguousarray(owner, dtype=np.int32), C.c_int32)))
         if with_coarse and N0 > 0 and device_galerkin:
             self.A0_device = np.empty((N0, N0)) if keep_A0 else None
             check(lib.ddm_galerkin_assemble(self.h, _p(self.A0_device, C.c_double) if keep_A0 else None))

@@ -12,7 +12,7 @@ BUILD_SH = os.path.join(os.path.dirname(_HERE), "csrc", "build.sh")
 SYMBOLS = [
     "ddm_last_error", "ddm_version", "ddm_ctx_create", "ddm_ctx_destroy", "ddm_comm_unique_id", "ddm_comm_init",
     "ddm_upload_operator", "ddm_upload_operator_bcsr3", "ddm_upload_halo", "ddm_upload_decomposition", "ddm_upload_factor", "ddm_upload_factor_lu", "ddm_factorize_subdomain", "ddm_upload_coarse",
-    "ddm_finalize", "ddm_set_deterministic", "ddm_blockdiag_solve", "ddm_seg_dot", "ddm_seg_axpby", "ddm_update_operator_values", "ddm_update_coarse_matrix", "ddm_galerkin_assemble", "ddm_vec_create", "ddm_vec_destroy", "ddm_vec_upload", "ddm_vec_download", "ddm_vec_fill",
+    "ddm_finalize", "ddm_set_deterministic", "ddm_blockdiag_solve", "ddm_seg_dot", "ddm_seg_axpby", "ddm_update_operator_values", "ddm_update_coarse_matrix", "ddm_galerkin_assemble", "ddm_set_coarse_coloring", "ddm_vec_create", "ddm_vec_destroy", "ddm_vec_upload", "ddm_vec_download", "ddm_vec_fill",
     "ddm_vec_copy", "ddm_vec_axpy", "ddm_vec_scale", "ddm_vec_add", "ddm_vec_xpay", "ddm_vec_device_ptr",
     "ddm_op_apply", "ddm_op_applyscaleadd", "ddm_dot", "ddm_norm", "ddm_schwarz_apply", "ddm_coarse_apply",
     "ddm_twolevel_apply", "ddm_pcg_solve", "ddm_gmres_solve", "ddm_gmres_solve_host", "ddm_op_apply_host", "ddm_op_applyscaleadd_host", "ddm_dot_host",

@@ -186,3 +186,33 @@ def galerkin_matrix_operands(subs, bases, n):
     )
     vals = np.concatenate([np.ascontiguousarray(b).ravel() for b in bases])
     return ks, off, sp.coo_matrix((vals, (rows, cols)), shape=(n, int(off[-1]))).tocsc()
+
+
+def coupling_coloring(A, subs):
+    """Colouring for the batched Galerkin product on the device (ddm_set_coarse_coloring): subdomains m and i are coupled when
+    A has an entry between their index sets (then block (m, i) of A0 = Z^T A Z can be non-zero -- the neighbour structure the
+    reference's build_solver exchanges, galerkin_preconditioner.hh:258-328); two subdomains may share a colour only if no
+    subdomain is coupled to both.  Greedy colouring of that "distance two" graph in subdomain order.
+    Returns (color int32[nsub], ncolors, owner_of int32[nsub, ncolors]: the subdomain of colour c coupled to m, or -1)."""
+    ns = len(subs)
+    n = A.shape[0]
+    memb = sp.csr_matrix((np.ones(sum(s.size for s in subs), dtype=np.float64), (np.concatenate(subs), np.repeat(np.arange(ns), [s.size for s in subs]))),
+                         shape=(n, ns))
+    pat = sp.csr_matrix((np.ones(A.nnz), A.indices, A.indptr), shape=A.shape)
+    C = ((memb.T @ (pat @ memb)) > 0).tocsr()  # coupled, self included
+    C = ((C + C.T) > 0).tocsr()
+    G2 = ((C.T @ C) > 0).tocsr()
+    color = np.full(ns, -1, dtype=np.int32)
+    for i in range(ns):
+        used = set(int(c) for c in color[G2.indices[G2.indptr[i] : G2.indptr[i + 1]]] if c >= 0)
+        c = 0
+        while c in used:
+            c += 1
+        color[i] = c
+    ncolors = int(color.max()) + 1 if ns else 0
+    owner = np.full((ns, ncolors), -1, dtype=np.int32)
+    for m in range(ns):
+        nb = C.indices[C.indptr[m] : C.indptr[m + 1]]
+        assert np.unique(color[nb]).size == nb.size  # by construction: at most one coupled subdomain per colour
+        owner[m, color[nb]] = nb
+    return color, ncolors, owner

@@ -60,6 +60,34 @@ def brick_ids(ncell, pgrid, group, lo, hi):
     return (blk * int(np.prod(per)) + loc).ravel()
 
 
+def brick_coloring(pgrid, group):
+    """Colouring of all bricks of the job for the batched Galerkin product (ddm_set_coarse_coloring): colour = brick coordinates
+    modulo 3, so two bricks of one colour are at least three bricks apart along some axis and no brick neighbours both (bricks
+    are coupled through A with their 26 neighbours only: an overlapping subdomain plus one matrix layer stays inside the
+    neighbouring bricks as long as overlap + 1 < brick width).  Brick ids follow decomp.box_partition's block-major numbering.
+    Returns (color int32[nsub], 27, owner_of int32[nsub, 27])."""
+    per = [p // g for p, g in zip(pgrid, group)]
+    b = np.stack(np.meshgrid(*[np.arange(p) for p in pgrid], indexing="ij"), -1).reshape(-1, 3)
+    blk = np.zeros(b.shape[0], dtype=np.int64)
+    loc = np.zeros(b.shape[0], dtype=np.int64)
+    for ax in range(3):
+        blk = blk * group[ax] + b[:, ax] // per[ax]
+        loc = loc * per[ax] + b[:, ax] % per[ax]
+    ids = blk * int(np.prod(per)) + loc
+    nsub = b.shape[0]
+    idgrid = np.empty(tuple(pgrid), dtype=np.int64)
+    idgrid[b[:, 0], b[:, 1], b[:, 2]] = ids
+    col_of = lambda q: (q[..., 0] % 3) * 9 + (q[..., 1] % 3) * 3 + (q[..., 2] % 3)
+    color = np.empty(nsub, dtype=np.int32)
+    color[ids] = col_of(b)
+    owner = np.full((nsub, 27), -1, dtype=np.int32)
+    for d in np.stack(np.meshgrid(*[np.arange(-1, 2)] * 3, indexing="ij"), -1).reshape(-1, 3):
+        q = b + d
+        ok = ((q >= 0) & (q < np.asarray(pgrid))).all(axis=1)
+        owner[ids[ok], col_of(q[ok])] = idgrid[q[ok, 0], q[ok, 1], q[ok, 2]]
+    return color, 27, owner
+
+
 def block_cells(ncell, pgrid, group, rank):
     """Cell box [lo, hi) of the block of bricks rank `rank` hosts."""
     per = [p // g for p, g in zip(pgrid, group)]

@@ -139,6 +139,15 @@ int ddm_finalize(ddm_ctx *ctx);
  * is then factored like an uploaded one.  A0_out (N0 x N0 row-major, may be NULL) receives a copy. */
 int ddm_galerkin_assemble(ddm_ctx *ctx, double *A0_out);
 
+/* Optional, before ddm_galerkin_assemble: a colouring of ALL subdomains of the job such that no subdomain is coupled through A to
+ * two subdomains of one colour (the reference's build_solver likewise touches neighbour blocks only,
+ * galerkin_preconditioner.hh:279-328).  The product then takes ncolors x max k_i passes instead of N0: the columns (i, k) of all
+ * subdomains i of a colour go through prolong -> A -> restrict together.  color[nsub_global], k_global[nsub_global] (basis sizes in
+ * global subdomain order), owner_of[m * ncolors + c] = the subdomain of colour c coupled to m (m itself included) or -1.
+ * nsub_global = 0 removes the colouring. */
+int ddm_set_coarse_coloring(ddm_ctx *ctx, int32_t nsub_global, int32_t ncolors, const int32_t *color, const int32_t *k_global,
+                            const int32_t *owner_of);
+
 /* ---- value updates with unchanged structure (Newton loops) -------------------------------
  * TwoLevelSchwarzSolver::apply keeps the overlapping index sets and only refreshes matrix values on every call after
  * the first (dune/ddm/twolevel_schwarz.hh:99-104).  Here: new operator values in the uploaded sparsity pattern; a

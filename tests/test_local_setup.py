@@ -52,3 +52,22 @@ def test_congruent_bricks_share_one_symbolic_analysis():
     assert len(L.factors) == 64 and len(ans) == 27  # per axis: first, inner, last brick; the 8 inner bricks differ by a translation only
     for F in L.factors:
         assert F.A.shape[0] == F.an.n
+
+
+def test_brick_coloring_covers_every_nonzero_galerkin_block():
+    """ddm_set_coarse_coloring's contract for the brick family: for every subdomain m and colour c at most one subdomain of colour
+    c has a non-zero Galerkin block with m, and owner_of names it (local.brick_coloring); checked against the dense A0 of the
+    one-process setup.  The generic colouring from the coupling graph (coarse.coupling_coloring) must satisfy the same."""
+    from ddm_b200.setup import coarse, local, problem
+
+    pg, g = (4, 4, 2), (2, 2, 1)
+    P = problem.poisson_q1_cube((20, 20, 10), pg, group=g, overlap=2, coarse="pou", workers=1)
+    off = np.concatenate(([0], np.cumsum([z.shape[1] for z in P.Z])))
+    for color, nc, owner in (local.brick_coloring(pg, g), coarse.coupling_coloring(P.A, P.subs)):
+        assert color.min() >= 0 and color.max() < nc and owner.shape == (P.nsub, nc)
+        for m in range(P.nsub):
+            assert owner[m, color[m]] == m
+            for i in range(P.nsub):
+                if np.abs(P.A0[off[m] : off[m + 1], off[i] : off[i + 1]]).max() > 0:
+                    assert owner[m, color[i]] == i, (m, i)
+    assert local.brick_coloring(pg, g)[1] == 27
