@@ -252,7 +252,7 @@ struct Segment {
     int32_t local0;   // start - base of the subdomain
 };
 
-__global__ void __launch_bounds__(256, 3) restrict_kernel(const Segment *__restrict__ segs, const int32_t *__restrict__ gidx,
+__global__ void __launch_bounds__(256, 4) restrict_kernel(const Segment *__restrict__ segs, const int32_t *__restrict__ gidx,
                                                           const double *__restrict__ d, double *__restrict__ W,
                                                           double *__restrict__ W2, int with_coarse,
                                                           const int64_t *__restrict__ zoff, const int32_t *__restrict__ sub_n,
