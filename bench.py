@@ -161,12 +161,14 @@ def _build_problem(a, world, fem, mesh, problem, **kw):
                                    coarse=a.coarse, nev=a.nev, meta=dict(mesh=f"kuhn-{shape}"), **kw)
 
 
-def build_local(a, world, rank, device):
+def build_local(a, world, rank, device, alone=False):
+    """alone: this process is the only one working (reference arm: the other ranks have exited), so it takes all host cores."""
     from ddm_b200.setup import local
 
     shape, _ = job_shape(a, world)
     pg, g = brick_grids(a, world)
-    return local.poisson_q1_cube_local(shape, pg, g, rank, overlap=a.overlap, coarse=a.coarse, nev=a.nev, workers=max(1, host_cores() // world),
+    return local.poisson_q1_cube_local(shape, pg, g, rank, overlap=a.overlap, coarse=a.coarse, nev=a.nev,
+                                       workers=host_cores() if alone else max(1, host_cores() // world),
                                        numeric=a.numeric, eigensolver=a.eigensolver, eig_device=device)
 
 
@@ -357,7 +359,7 @@ def run_reference(a):
 
     nthreads = host_cores()
     if use_local_setup(a):
-        L = build_local(a, world, 0, local)
+        L = build_local(a, world, 0, local, alone=True)
         L.k_all = np.array([z.shape[1] for z in L.Z] * world, dtype=np.int64)  # the other blocks carry the same counts (nev each)
         n, nsub, N0 = L.n_global, L.nsub_global, int(L.k_all.sum())
         if world == 1:
