@@ -285,6 +285,66 @@ static int dev_upload(T **dst, const T *src, size_t count)
     return 0;
 }
 
+// ------------------------------------------------------------------------------------------------ entry point without allocation
+// ddm_dot_noalloc (include/ddm_b200.h): the dot product for callers that cannot allocate -- code under CUDA graph capture, tight
+// serving loops, harnesses that forbid cudaMalloc.  No counterpart in the reference.
+// ddm_dot keeps its per-block partial sums in a cudaMalloc'ed array of the context; this variant keeps them in the file-scope
+// array below, which every GPU that loads the library holds until the process exits (kNoAllocMaxPartials doubles = 128 KB).
+// One block reduces one chunk of kNoAllocChunk elements, so the array bounds the vector length:
+// n <= kNoAllocMaxPartials * kNoAllocChunk = 134 217 728 entries (1 GiB per vector); longer vectors are refused.
+// The array is shared by every call on a GPU and keeps the last call's contents.  Nothing in it has to start at zero: a call
+// writes partials [0, nblk) in its first kernel and reads exactly those in its second.  Calls that overlap on one GPU (two
+// streams, two contexts, two processes' worth of threads on one context) race on it; calls on one stream are ordered.
+constexpr int kNoAllocChunk = 8192;
+constexpr int kNoAllocMaxPartials = 16384;
+constexpr int kNoAllocMaxDevices = 64;
+static __device__ __align__(256) double g_noalloc_scratch[kNoAllocMaxPartials];
+// In host code `g_noalloc_scratch` is only a stand-in for the symbol, not a device address: the address is looked up once per
+// device (noalloc_setup, from ddm_ctx_create with that device current) and that pointer is what the kernels are given.
+static double *g_noalloc_ptr[kNoAllocMaxDevices] = {nullptr};
+
+__global__ void __launch_bounds__(256) dot_chunk_kernel(int64_t n, const double *__restrict__ x, const double *__restrict__ y,
+                                                        double *__restrict__ partial)
+{
+    __shared__ double sm[8];
+    const int64_t base = (int64_t)blockIdx.x * kNoAllocChunk;
+    double acc = 0.0;
+#pragma unroll 4
+    for (int k = threadIdx.x; k < kNoAllocChunk; k += 256) {
+        const int64_t i = base + k;
+        if (i < n) acc = fma(x[i], y[i], acc);
+    }
+    const double t = block_sum_256(acc, sm);
+    if (threadIdx.x == 0) partial[blockIdx.x] = t;
+}
+
+static int noalloc_setup(int device)  // the caller has made `device` current
+{
+    if (device < 0 || device >= kNoAllocMaxDevices) return fail("ddm_dot_noalloc supports device ordinals below %d", kNoAllocMaxDevices);
+    if (g_noalloc_ptr[device]) return 0;
+    void *p = nullptr;
+    CU(cudaGetSymbolAddress(&p, g_noalloc_scratch));
+    if (!p) return fail("cudaGetSymbolAddress returned a null address for the no-allocation scratch array");
+    g_noalloc_ptr[device] = static_cast<double *>(p);
+    return 0;
+}
+
+struct ddm_ctx;
+static int noalloc_launch(ddm_ctx *c, int64_t n, const double *x, const double *y, double *out);
+
+extern "C" int ddm_dot_noalloc(ddm_ctx *c, int64_t n, const double *x, const double *y, double *out)
+{
+    constexpr int64_t kMaxN = (int64_t)kNoAllocMaxPartials * kNoAllocChunk;
+    if (!c) return fail("ddm_dot_noalloc: null context");
+    if (n < 0) return fail("ddm_dot_noalloc: negative length %lld", (long long)n);
+    if (n > kMaxN)
+        return fail("ddm_dot_noalloc: n = %lld exceeds the maximum of %lld entries (%d partial sums of %d entries in the static scratch array); "
+                    "use ddm_dot for longer vectors",
+                    (long long)n, (long long)kMaxN, kNoAllocMaxPartials, kNoAllocChunk);
+    if (!out || (n > 0 && (!x || !y))) return fail("ddm_dot_noalloc: null device pointer");
+    return noalloc_launch(c, n, x, y, out);
+}
+
 struct DevGuard {  // frees the temporaries of a setup routine on every return path
     std::vector<void *> ptrs;
     ~DevGuard()
@@ -294,6 +354,16 @@ struct DevGuard {  // frees the temporaries of a setup routine on every return p
     void own(const void *p) { ptrs.push_back(const_cast<void *>(p)); }
 };
 
+static int noalloc_launch(ddm_ctx *c, int64_t n, const double *x, const double *y, double *out)
+{
+    double *scratch = g_noalloc_ptr[c->device];  // device address from cudaGetSymbolAddress, never the symbol itself
+    if (!scratch) return fail("ddm_dot_noalloc: no scratch address for device %d (context not created by ddm_ctx_create?)", c->device);
+    const int nblk = (int)((n + kNoAllocChunk - 1) / kNoAllocChunk);
+    if (nblk > 0) LAUNCH(c, dot_chunk_kernel, nblk, 256, n, x, y, scratch);
+    LAUNCH(c, reduce_final_kernel, 1, 256, nblk, scratch, out);  // fixed tree over partials [0, nblk); nblk = 0 gives 0
+    return 0;
+}
+
 extern "C" int ddm_ctx_create(int device, ddm_ctx **out)
 {
     int ndev = 0;
@@ -302,6 +372,7 @@ extern "C" int ddm_ctx_create(int device, ddm_ctx **out)
         return fail("ddm_b200 needs a CUDA device (sm_100a); none found: %s", cudaGetErrorString(e));
     if (device < 0 || device >= ndev) return fail("device %d out of range (have %d)", device, ndev);
     CU(cudaSetDevice(device));
+    CK(noalloc_setup(device));  // once per device, with it current: device address of the static scratch of ddm_dot_noalloc
     ddm_ctx *c = new ddm_ctx();
     c->device = device;
     cudaDeviceProp prop;

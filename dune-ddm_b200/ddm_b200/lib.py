@@ -14,7 +14,7 @@ SYMBOLS = [
     "ddm_upload_operator", "ddm_upload_operator_bcsr3", "ddm_upload_halo", "ddm_upload_decomposition", "ddm_upload_factor", "ddm_upload_factor_lu", "ddm_factorize_subdomain", "ddm_upload_coarse",
     "ddm_finalize", "ddm_set_deterministic", "ddm_blockdiag_solve", "ddm_seg_dot", "ddm_seg_axpby", "ddm_update_operator_values", "ddm_update_coarse_matrix", "ddm_galerkin_assemble", "ddm_set_coarse_coloring", "ddm_vec_create", "ddm_vec_destroy", "ddm_vec_upload", "ddm_vec_download", "ddm_vec_fill",
     "ddm_vec_copy", "ddm_vec_axpy", "ddm_vec_scale", "ddm_vec_add", "ddm_vec_xpay", "ddm_vec_device_ptr",
-    "ddm_op_apply", "ddm_op_applyscaleadd", "ddm_dot", "ddm_norm", "ddm_schwarz_apply", "ddm_coarse_apply",
+    "ddm_op_apply", "ddm_op_applyscaleadd", "ddm_dot", "ddm_dot_noalloc", "ddm_norm", "ddm_schwarz_apply", "ddm_coarse_apply",
     "ddm_twolevel_apply", "ddm_pcg_solve", "ddm_gmres_solve", "ddm_gmres_solve_host", "ddm_op_apply_host", "ddm_op_applyscaleadd_host", "ddm_dot_host",
     "ddm_twolevel_apply_host", "ddm_pcg_solve_host", "ddm_host_register", "ddm_host_unregister", "ddm_get_stat", "ddm_timers_enable", "ddm_timers_reset",
     "ddm_get_timer", "ddm_stopwatch_start", "ddm_stopwatch_stop", "ddm_kernel_launches", "ddm_profiler_range", "ddm_sync",

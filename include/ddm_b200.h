@@ -191,6 +191,17 @@ int ddm_op_applyscaleadd(ddm_ctx *ctx, double alpha, ddm_vec *x, ddm_vec *y);
 int ddm_dot(ddm_ctx *ctx, const ddm_vec *x, const ddm_vec *y, double *out);
 int ddm_norm(ddm_ctx *ctx, const ddm_vec *x, double *out);
 
+/* Dot product without any allocation.  NO COUNTERPART IN THE REFERENCE: added for callers
+ * that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same sum as
+ * ddm_dot over the first n entries of two device arrays, result stored in *out ON THE DEVICE (no host synchronisation); runs on
+ * the context's stream.  x, y, out are device pointers on the context's GPU (e.g. ddm_vec_device_ptr).  Rank-local: with several
+ * ranks the caller adds the per-rank results.  The call allocates and frees nothing: its per-block partial sums live in a static
+ * device array of 16 384 doubles (128 KB, held by every GPU that loads the library until the process exits), one partial per
+ * chunk of 8 192 entries, so n is limited to 134 217 728 entries; a longer vector is refused with an error (use ddm_dot).
+ * All calls on a GPU share that array and it keeps the last call's contents (a call only reads what it has just written, so
+ * nothing needs clearing); calls that overlap on the GPU -- other streams, other contexts -- race on it. */
+int ddm_dot_noalloc(ddm_ctx *ctx, int64_t n, const double *x, const double *y, double *out);
+
 /* ---- preconditioners ------------------------------------------------------------------- */
 /* SchwarzPreconditioner::apply, dune/ddm/schwarz.hh:115-149. */
 int ddm_schwarz_apply(ddm_ctx *ctx, int schwarz_type, ddm_vec *d, ddm_vec *x);
