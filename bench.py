@@ -270,11 +270,12 @@ def host_products(ctx, L, subset=None):
     return SetupProducts(A=A, b=b, owner=np.zeros(S.n_own, dtype=np.int32), subs=subs, pou=pou, factors=factors, Z=Z, A0=A0, meta=dict(L.meta))
 
 
-def cpu_arm(a, world, ctx, L=None, P=None, its_hint=None, budget_s=30.0, nthreads=None):
+def cpu_arm(a, world, ctx, L=None, P=None, its_hint=None, budget_s=30.0, nthreads=None, steps=1):
     """Times the CPU oracle (all host threads) on the workload.  Whole problem when its factors fit in host memory (N = 1):
     PCG itself, first m iterations, extrapolated by apply count.  Otherwise a bounded sample: the subdomain solves of a subset
     of this rank's subdomains plus full-length vector passes, extrapolated by factor entries and by the number of GPUs' shares.
-    Returns (seconds per solve, iterations or None, description)."""
+    steps: how many samples are timed (their mean is returned); the budget is shared between them.
+    Returns (seconds per solve, iterations or None, converged or None, description, oracle)."""
     from oracle import oracle
 
     nthreads = nthreads or host_cores()
@@ -297,12 +298,18 @@ def cpu_arm(a, world, ctx, L=None, P=None, its_hint=None, budget_s=30.0, nthread
             t_once = time.perf_counter() - t0
         else:
             its, conv, t_once = int(its_hint), True, None
-        m = int(max(1, min(its, budget_s / max(t1 / 2, 1e-9))))
-        t0 = time.perf_counter()
-        _, it, _, _ = O.pcg(P.b, reduction=REDUCTION, maxit=m)
-        t = time.perf_counter() - t0
-        t_full = t * (its + 1) / (it + 1)  # it iterations cost it + 1 applies
-        desc = f"first {it} of {its} PCG iterations of the same solve ({t:.1f} s measured, extrapolated by apply count)"
+        steps = max(1, int(steps))
+        m = int(max(1, min(its, budget_s / steps / max(t1 / 2, 1e-9) - 1)))  # m iterations cost m + 1 applies
+        ts, t_sum = [], 0.0
+        for _ in range(steps):
+            t0 = time.perf_counter()
+            _, it, _, _ = O.pcg(P.b, reduction=REDUCTION, maxit=m)
+            t = time.perf_counter() - t0
+            t_sum += t
+            ts.append(t * (its + 1) / (it + 1))  # it iterations cost it + 1 applies
+        t_full = float(np.mean(ts))
+        each = "" if steps == 1 else f"each of {steps} steps = "
+        desc = f"{each}first {it} of {its} PCG iterations of the same solve ({t_sum:.1f} s measured in all, extrapolated by apply count)"
         if t_once is not None:
             desc += f"; full solve measured once: {t_once:.1f} s"
         return t_full, its, bool(conv), desc, O
@@ -324,7 +331,7 @@ def cpu_arm(a, world, ctx, L=None, P=None, its_hint=None, budget_s=30.0, nthread
     d = np.random.default_rng(0).standard_normal(Ps.n)
     O.twolevel_apply(d)
     reps, t_app = 0, 0.0
-    while t_app < budget_s / 2 and reps < 20:
+    while (t_app < budget_s / 2 and reps < 20) or reps < min(int(steps), 20):  # at least `steps` timed applications (capped at 20)
         t0 = time.perf_counter()
         O.twolevel_apply(d)
         t_app += time.perf_counter() - t0
@@ -341,7 +348,7 @@ def cpu_arm(a, world, ctx, L=None, P=None, its_hint=None, budget_s=30.0, nthread
     share = nnz.sum() / nnz[pick].sum()
     t_iter = (t_app * share + t_vec) * world  # the other GPUs' shares are congruent blocks of the same cube
     its = int(its_hint) if its_hint is not None else None
-    desc = (f"subdomain solves of {len(pick)} of {L.nsub * world} subdomains ({100 / share / world:.1f} % of the factor entries) + SpMV and vector passes of one GPU's "
+    desc = (f"{reps} timed applications; subdomain solves of {len(pick)} of {L.nsub * world} subdomains ({100 / share / world:.1f} % of the factor entries) + SpMV and vector passes of one GPU's "
             f"share, extrapolated by factor entries and x{world} shares; {t_iter:.2f} s per PCG iteration")
     return t_iter, its, None, desc, O
 
@@ -371,7 +378,7 @@ def run_reference(a):
             L1.shard = copy.copy(L.shard)
             L1.shard.world, L1.shard.rank = 1, 0
             ctx = api.Context.from_local(L1, device=local, with_coarse=False)
-        t_solve, its, conv, desc, _ = cpu_arm(a, world, ctx, L=L, budget_s=30.0, nthreads=nthreads)
+        t_solve, its, conv, desc, _ = cpu_arm(a, world, ctx, L=L, budget_s=60.0, nthreads=nthreads, steps=a.steps)
         ctx.close()
         if its is None:  # bounded sample: no CPU solve of the whole job exists; iteration count of this family (flat from 1 to 8 GPUs)
             its = int(os.environ.get("DDM_BENCH_ASSUME_ITS", ASSUMED_ITERATIONS))
@@ -383,7 +390,7 @@ def run_reference(a):
         n, nsub, N0 = P.n, P.nsub, P.A0.shape[0]
         if any(hasattr(F, "an") for F in P.factors):
             P.factors = [F.host() if hasattr(F, "an") else F for F in P.factors]
-        t_solve, its, conv, desc, _ = cpu_arm(a, world, None, P=P, budget_s=30.0, nthreads=nthreads)
+        t_solve, its, conv, desc, _ = cpu_arm(a, world, None, P=P, budget_s=60.0, nthreads=nthreads, steps=a.steps)
     val = n / t_solve / 1e6
     line = {"impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": a.gpus, "steps": a.steps, "warmup": a.warmup,
             "ms_per_step": t_solve * 1e3, "higher_is_better": True, "scaling": "strong" if a.strong else "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",

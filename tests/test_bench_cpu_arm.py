@@ -60,3 +60,14 @@ def test_both_arms_emit_the_same_config(setting):
     c1 = bench.config_of(a, 1, L.n_global, L.nsub_global, int(L.k_all.sum()))
     c2 = bench.config_of(a, 1, L.n_global, L.nsub_global, int(L.k_all.sum()))
     assert c1 == c2 and set(c1) == {"workload", "dofs", "subdomains", "coarse_dim", "l2_policy"} and "brick subdomains" in c1["workload"]
+
+
+def test_reference_arm_times_as_many_samples_as_steps(setting, monkeypatch):
+    """--impl reference --steps K: K bounded samples are timed (whole-problem mode: K short PCG runs; sample mode: at least K
+    applications), so the line's `steps` says what was done."""
+    bench, a, L = setting
+    t, its, conv, desc, _ = bench.cpu_arm(a, 1, NoDevice(), L=L, budget_s=1.0, nthreads=2, steps=3)
+    assert conv and t > 0 and "each of 3 steps" in desc
+    monkeypatch.setattr(bench, "mem_available_bytes", lambda: 0)
+    t_iter, _, _, desc, _ = bench.cpu_arm(a, 1, NoDevice(), L=L, its_hint=12, budget_s=0.0, nthreads=2, steps=4)
+    assert t_iter > 0 and desc.startswith("4 timed applications")
