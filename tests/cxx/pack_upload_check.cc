@@ -129,6 +129,9 @@ int main(int argc, char **argv)
   } catch (Dune::Exception &e) {
     std::fprintf(stderr, "Dune::Exception: %s\n", e.what());
     return 1;
+  } catch (std::exception &e) {  // the pack reader refuses damaged or foreign files with std::runtime_error
+    std::fprintf(stderr, "error: %s\n", e.what());
+    return 4;
   }
   // dump: [u64 name length][name][u64 byte count][bytes] ...
   std::FILE *fh = std::fopen(argv[2], "wb");

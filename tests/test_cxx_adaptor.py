@@ -98,3 +98,41 @@ def test_block3_pack_matches_scipy_bsr(checker, elast, tmp_path):
     # the adaptor keeps every block the scalar pattern touches; scipy does the same (explicit zeros stay in the pattern)
     assert np.array_equal(rp, B.indptr) and np.array_equal(ci, B.indices) and np.array_equal(va, B.data)
     check_factors(d, P)
+
+
+def _locate(raw, name):
+    """Offsets of (element code, rank, first dimension) of array `name` in a .ddmpack byte string (layout: setup/pack.py)."""
+    key = struct.pack("<i", len(name)) + name.encode()
+    o = raw.index(key) + len(key)
+    return o, o + 4, o + 8
+
+
+def test_damaged_packs_are_refused(checker, small3d, tmp_path):
+    """the C++ reader must not trust the file -- a truncated pack, an unknown element code, a dimension larger than the
+    file and an array of the wrong element type each end in an error message, not in an out-of-bounds read."""
+    from ddm_b200.setup import pack
+
+    src = str(tmp_path / "good.ddmpack")
+    pack.save_products(src, small3d)
+    good = open(src, "rb").read()
+    code_o, ndim_o, dim_o = _locate(good, "A_rowptr")
+    assert struct.unpack_from("<i", good, code_o)[0] == 2 and struct.unpack_from("<i", good, ndim_o)[0] == 1
+
+    def run(raw):
+        bad = str(tmp_path / "bad.ddmpack")
+        open(bad, "wb").write(raw)
+        return subprocess.run([checker, bad, str(tmp_path / "bad.dump")], capture_output=True, text=True, timeout=120)
+
+    cases = {
+        "truncated": (good[: len(good) // 2], "ddmpack"),
+        "unknown element code": (good[:code_o] + struct.pack("<i", 9) + good[code_o + 4 :], "unknown element type"),
+        "dimension beyond the file": (good[:dim_o] + struct.pack("<q", 1 << 50) + good[dim_o + 8 :], "larger than the file"),
+        "negative dimension": (good[:dim_o] + struct.pack("<q", -5) + good[dim_o + 8 :], "larger than the file"),
+        "wrong element type": (good[:code_o] + struct.pack("<i", 0) + good[code_o + 4 :], "wrong element type"),  # f64 has the same width
+        "foreign file": (b"NOTAPACK" + good[8:], "not a .ddmpack"),
+    }
+    for what, (raw, text) in cases.items():
+        r = run(raw)
+        assert r.returncode == 4, (what, r.returncode, r.stderr[-300:])
+        assert text in r.stderr, (what, r.stderr[-300:])
+    assert run(good).returncode == 0
