@@ -111,3 +111,60 @@ def test_bench_sharded_setup_under_torchrun(tmp_path, extra):
         if r.returncode == 0 or "AssertionError" in r.stderr:
             break
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-3000:]
+
+
+LOCAL_WORKER = r"""
+import os, sys
+sys.path.insert(0, {root!r}); sys.path.insert(0, os.path.join({root!r}, "dune-ddm_b200"))
+import torch.distributed as dist, numpy as np
+import bench
+sys.argv = ["bench.py", "--ncell", "8", "--nsub", "8", "--gpus", os.environ["WORLD_SIZE"], "--eigensolver", "host", "--numeric", "host", "--nev", "4"]
+a = bench.parse()
+rank, world, local = bench.dist_env()
+assert bench.use_local_setup(a)  # the bench's default path for the Q1 brick family
+dist.init_process_group("gloo")
+L = bench.build_local(a, world, rank, 0)
+mine = [int(z.shape[1]) for z in L.Z]
+ks = [None] * world
+dist.all_gather_object(ks, mine)
+L.k_all = np.concatenate([np.asarray(k, dtype=np.int64) for k in ks])
+S = L.shard
+assert S.rank == rank and S.world == world and len(L.factors) == 8 and L.nsub_global == 8 * world
+assert L.k_all.size == L.nsub_global and int(L.k_all[S.sub_range[0]:S.sub_range[1]].sum()) == sum(mine)
+# every DOF has exactly one owner, and what rank r sends to q is what q expects from r, id by id
+info = [None] * world
+sends = {{int(p): S.owned[S.send_idx[S.send_ptr[i]:S.send_ptr[i + 1]]] for i, p in enumerate(S.peers)}}
+recvs = {{int(p): S.ghosts[S.recv_ptr[i]:S.recv_ptr[i + 1]] for i, p in enumerate(S.peers)}}
+dist.all_gather_object(info, dict(owned=S.owned, sends=sends, recvs=recvs, n=L.n_global))
+allowned = np.concatenate([i["owned"] for i in info])
+assert allowned.size == L.n_global and np.unique(allowned).size == L.n_global
+for q, other in enumerate(info):
+    if q == rank:
+        continue
+    mine_to_q = sends.get(q, np.zeros(0, dtype=np.int64))
+    q_from_me = other["recvs"].get(rank, np.zeros(0, dtype=np.int64))
+    assert np.array_equal(mine_to_q, q_from_me), (rank, q)
+name = bench.workload_name(a, world)
+assert "brick subdomains" in name
+dist.barrier()
+"""
+
+
+@pytest.mark.timeout(300)
+def test_bench_rank_local_setup_under_torchrun(tmp_path):
+    """bench.py's default N > 1 wiring on the CPU: four ranks (gloo) each build their own region (setup/local.py), exchange only
+    the coarse-vector counts, and their halo plans fit together: every DOF has one owner, and the ids rank r sends to rank q
+    are exactly, and in the same order, the ghost ids q expects from r."""
+    import socket
+
+    script = tmp_path / "local_worker.py"
+    script.write_text(LOCAL_WORKER.format(root=os.path.dirname(HERE)))
+    for attempt in range(2):
+        with socket.socket() as s:
+            s.bind(("127.0.0.1", 0))
+            port = s.getsockname()[1]
+        r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=4", "--master-addr", "127.0.0.1",
+                            "--master-port", str(port), str(script)], capture_output=True, text=True, timeout=200)
+        if r.returncode == 0 or "AssertionError" in r.stderr:
+            break
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-3000:]
